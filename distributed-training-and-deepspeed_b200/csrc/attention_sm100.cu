@@ -1,0 +1,669 @@
+// Fused multi-head attention forward + backward on tcgen05 / TMEM / TMA (head_dim 64, bf16).
+//
+//   S = scale * Q·Kᵀ (+ ALiBi) (+ key padding bias) (causal mask) ; P = softmax(S) ; O = drop(P)·V
+//
+// Replaces bmm -> Softmax -> Dropout -> bmm (model/transformer.py:80-86 in the reference) and
+// HF BertSelfAttention / BLOOM / OPT attention: the [B·heads,S,S]
+// score matrix never touches HBM.  Q, K, V are read straight out of the fused QKV projection
+// output [B·S, 3H] through one TMA tensor map (no head-major transposes), and the context is
+// written token-major [B·S, H] ready for the output projection GEMM.
+//
+// Three kernels, all 6 warps: warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM owner),
+// warps 2..5 = 128 softmax threads, one per TMEM lane (= one score-matrix row each):
+//   attn_fwd_kernel      CTA = (128 queries, head); loops over key blocks, online softmax.
+//   attn_bwd_dq_kernel   CTA = (128 queries, head); recomputes P, dS -> dQ.
+//   attn_bwd_dkdv_kernel CTA = (128 keys,    head); works on Sᵀ so that Pᵀ and dSᵀ come out of
+//                        TMEM row-per-thread and can feed dV += Pᵀ·dO, dK += dSᵀ·Q directly.
+// P / dS tiles are staged in shared memory in the 128B-swizzled K-major layout TMA would have
+// produced, so the same smem descriptors serve TMA-loaded and thread-written operands.  A
+// [128 x 64] bf16 tile loaded by TMA is used both as a K-major operand and, reinterpreted, as an
+// MN-major one (e.g. K_j as B of Q·Kᵀ and as B of dS·K) — the bytes are identical.
+// The backward is deterministic (no atomics): dQ has its own kernel.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "dtds_b200.h"
+#include "internal.h"
+
+namespace dtds {
+
+constexpr int kAttnThreads = 192;
+constexpr int kTile = 128 * 64 * 2;  // one [128 x 64] bf16 tile = 16 KiB
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+struct AttnParams {
+  int B, S, heads, H;
+  float scale;
+  int causal;
+  const float* key_bias;  // [B, S] additive bias per key (padding mask) or null
+  const float* alibi;     // [heads] slopes or null
+  float p_drop;
+  unsigned long long seed;
+  __nv_bfloat16* out;  // fwd: [B*S, H]
+  float* lse;          // [B, heads, S] natural-log logsumexp of the biased, scaled scores
+  const float* delta;  // bwd: [B, heads, S] rowsum(dO * O)
+  __nv_bfloat16* dqkv;  // bwd: [B*S, 3H]
+};
+
+__device__ __forceinline__ float attn_keep(const AttnParams& p, int bh, int iq, int jk,
+                                           float inv_keep) {
+  if (p.p_drop <= 0.f) return 1.f;
+  const uint64_t idx = (static_cast<uint64_t>(bh) * p.S + iq) * p.S + jk;
+  const float u = (hash_u32(p.seed, idx) >> 8) * (1.0f / 16777216.0f);
+  return u >= p.p_drop ? inv_keep : 0.f;
+}
+
+// Writes 32 consecutive columns [col0, col0+32) of row `row` of a [128 x 128] bf16 operand tile
+// held as two 128B-swizzled [128 x 64] atoms (the layout TMA SWIZZLE_128B produces).
+__device__ __forceinline__ void store_chunk_sw128(uint8_t* tile, int row, int col0,
+                                                  const float (&v)[32]) {
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    const int col = col0 + g * 8;
+    const int atom = col >> 6;
+    const int ch = (col & 63) >> 3;
+    uint8_t* dst = tile + atom * kTile + row * 128 + ((ch ^ (row & 7)) << 4);
+    *reinterpret_cast<uint4*>(dst) =
+        make_uint4(pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]), pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]),
+                   pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]));
+  }
+}
+
+__device__ __forceinline__ uint64_t kdesc(const uint8_t* tile, int kk) {  // K-major, 16-wide k step
+  return make_smem_desc_sw128(smem_u32(tile) + kk * 32, 16, 1024);
+}
+__device__ __forceinline__ uint64_t kdesc128(const uint8_t* tile, int kk) {  // two-atom K=128 tile
+  return make_smem_desc_sw128(smem_u32(tile) + (kk >> 2) * kTile + (kk & 3) * 32, 16, 1024);
+}
+__device__ __forceinline__ uint64_t mndesc(const uint8_t* tile, int kk) {  // MN-major view
+  return make_smem_desc_sw128(smem_u32(tile) + kk * 2048, 8192, 1024);
+}
+
+__device__ __forceinline__ void check_smem_alignment(const void* smem) {
+  if (threadIdx.x == 0 && (smem_u32(smem) & 1023u) != 0) {
+    printf("[dtds] attention: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+}
+
+// ============================================================================== forward
+__global__ void __launch_bounds__(kAttnThreads)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sQ = smem;
+  uint8_t* sKV = smem + kTile;          // 2 stages x (K | V)
+  uint8_t* sP = smem + kTile + 4 * kTile;  // [128 x 128] bf16
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kTile);
+  uint64_t* q_full = bars;
+  uint64_t* kv_full = bars + 1;
+  uint64_t* kv_empty = bars + 3;
+  uint64_t* s_full = bars + 5;
+  uint64_t* p_full = bars + 6;
+  uint64_t* o_full = bars + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  check_smem_alignment(smem);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qb = blockIdx.x, bh = blockIdx.y;
+  const int b = bh / p.heads, h = bh % p.heads;
+  const int row0 = b * p.S;
+  const int nkv = p.causal ? qb + 1 : p.S / 128;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_qkv);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    mbar_init(s_full, 1);
+    mbar_init(p_full, 4);
+    mbar_init(o_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_slot, 256); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tO = tmem + 128;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(q_full, kTile);
+      tma_load_2d(sQ, &tm_qkv, q_full, h * 64, row0 + qb * 128, kEvictNormal);
+      for (int j = 0; j < nkv; ++j) {
+        const int st = j & 1;
+        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&kv_full[st], 2 * kTile);
+        tma_load_2d(sKV + st * 2 * kTile, &tm_qkv, &kv_full[st], p.H + h * 64, row0 + j * 128, kEvictLast);
+        tma_load_2d(sKV + st * 2 * kTile + kTile, &tm_qkv, &kv_full[st], 2 * p.H + h * 64, row0 + j * 128, kEvictLast);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_qk = make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);
+      mbar_wait(q_full, 0);
+      for (int j = 0; j < nkv; ++j) {
+        const int st = j & 1;
+        const uint8_t* sK = sKV + st * 2 * kTile;
+        const uint8_t* sV = sK + kTile;
+        mbar_wait(&kv_full[st], (j >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) umma_ss(tS, kdesc(sQ, kk), kdesc(sK, kk), idesc_qk, kk > 0);
+        umma_commit(s_full);
+        mbar_wait(p_full, j & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_ss(tO, kdesc128(sP, kk), mndesc(sV, kk), idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&kv_empty[st]);
+        umma_commit(o_full);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const int iq = qb * 128 + r;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    const float scale_l2 = p.scale * kLog2e;
+    const float slope_l2 = p.alibi != nullptr ? p.alibi[h] * kLog2e : 0.f;
+    const float inv_keep = p.p_drop > 0.f ? 1.f / (1.f - p.p_drop) : 1.f;
+    const float* kb = p.key_bias != nullptr ? p.key_bias + static_cast<size_t>(b) * p.S : nullptr;
+    float m = -INFINITY, l = 0.f;
+    uint32_t regs[32];
+    float v[32];
+    for (int j = 0; j < nkv; ++j) {
+      mbar_wait(s_full, j & 1);
+      tc_fence_after();
+      auto score = [&](uint32_t raw, int jk) -> float {
+        float x = __uint_as_float(raw) * scale_l2;
+        if (p.alibi != nullptr) x += slope_l2 * static_cast<float>(jk - iq);
+        if (kb != nullptr) x += kb[jk] * kLog2e;
+        if (p.causal && jk > iq) x = -INFINITY;
+        return x;
+      };
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        tmem_ld_32x32(tS + lane_off + c * 32, regs);
+        tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < 32; ++t) mx = fmaxf(mx, score(regs[t], j * 128 + c * 32 + t));
+      }
+      const float m_new = fmaxf(m, mx);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float corr = exp2f(m - m_use);
+      if (j > 0) {  // previous P·V must have finished reading sP and updating O
+        mbar_wait(o_full, (j - 1) & 1);
+        tc_fence_after();
+      }
+      float rs = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        tmem_ld_32x32(tS + lane_off + c * 32, regs);
+        tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+          const int jk = j * 128 + c * 32 + t;
+          const float pr = exp2f(score(regs[t], jk) - m_use);
+          rs += pr;
+          v[t] = pr * attn_keep(p, bh, iq, jk, inv_keep);
+        }
+        store_chunk_sw128(sP, r, c * 32, v);
+      }
+      l = l * corr + rs;
+      m = m_new;
+      if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          tmem_ld_32x32(tO + lane_off + c * 32, regs);
+          tmem_ld_wait();
+#pragma unroll
+          for (int t = 0; t < 32; ++t) regs[t] = __float_as_uint(__uint_as_float(regs[t]) * corr);
+          tmem_st_32x32(tO + lane_off + c * 32, regs);
+        }
+        tmem_st_wait();
+      }
+      fence_async_shared();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);
+    }
+    mbar_wait(o_full, (nkv - 1) & 1);
+    tc_fence_after();
+    const float inv_l = l > 0.f ? 1.f / l : 0.f;
+    __nv_bfloat16* dst = p.out + static_cast<size_t>(row0 + iq) * p.H + h * 64;
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+      tmem_ld_32x32(tO + lane_off + c * 32, regs);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float o[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) o[t] = __uint_as_float(regs[g * 8 + t]) * inv_l;
+        *reinterpret_cast<uint4*>(dst + c * 32 + g * 8) =
+            make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
+                       pack_bf16x2(o[6], o[7]));
+      }
+    }
+    if (p.lse != nullptr)
+      p.lse[static_cast<size_t>(bh) * p.S + iq] = (l > 0.f) ? (m * kLn2 + __logf(l)) : -INFINITY;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc(tmem, 256);
+}
+
+// ============================================================================== backward: delta
+// delta[b,h,s] = sum_d dO[b,s,h,d] * O[b,s,h,d].  One warp per token.
+__global__ void __launch_bounds__(256)
+attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                  float* __restrict__ delta, int B, int S, int heads) {
+  const int tok = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (tok >= B * S) return;
+  const int lane = threadIdx.x & 31;
+  const int b = tok / S, s = tok % S;
+  const int H = heads * 64;
+  for (int h = 0; h < heads; ++h) {
+    const size_t off = static_cast<size_t>(tok) * H + h * 64 + lane * 2;
+    const uint32_t a = *reinterpret_cast<const uint32_t*>(o + off);
+    const uint32_t g = *reinterpret_cast<const uint32_t*>(d_o + off);
+    float acc = bf16_lo(a) * bf16_lo(g) + bf16_hi(a) * bf16_hi(g);
+    acc = warp_sum(acc);
+    if (lane == 0) delta[(static_cast<size_t>(b) * heads + h) * S + s] = acc;
+  }
+}
+
+// ============================================================================== backward: dQ
+__global__ void __launch_bounds__(kAttnThreads)
+attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
+                   const AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sQ = smem;
+  uint8_t* sdO = smem + kTile;
+  uint8_t* sKV = smem + 2 * kTile;   // 2 stages x (K | V)
+  uint8_t* sdS = smem + 6 * kTile;   // [128 q x 128 keys]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + 2 * kTile);
+  uint64_t* q_full = bars;
+  uint64_t* kv_full = bars + 1;
+  uint64_t* kv_empty = bars + 3;
+  uint64_t* s_full = bars + 5;
+  uint64_t* ds_full = bars + 6;
+  uint64_t* dq_done = bars + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  check_smem_alignment(smem);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qb = blockIdx.x, bh = blockIdx.y;
+  const int b = bh / p.heads, h = bh % p.heads;
+  const int row0 = b * p.S;
+  const int nkv = p.causal ? qb + 1 : p.S / 128;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_do);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    mbar_init(s_full, 1);
+    mbar_init(ds_full, 4);
+    mbar_init(dq_done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tdP = tmem + 128, tdQ = tmem + 256;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(q_full, 2 * kTile);
+      tma_load_2d(sQ, &tm_qkv, q_full, h * 64, row0 + qb * 128, kEvictNormal);
+      tma_load_2d(sdO, &tm_do, q_full, h * 64, row0 + qb * 128, kEvictNormal);
+      for (int j = 0; j < nkv; ++j) {
+        const int st = j & 1;
+        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&kv_full[st], 2 * kTile);
+        tma_load_2d(sKV + st * 2 * kTile, &tm_qkv, &kv_full[st], p.H + h * 64, row0 + j * 128, kEvictLast);
+        tma_load_2d(sKV + st * 2 * kTile + kTile, &tm_qkv, &kv_full[st], 2 * p.H + h * 64, row0 + j * 128, kEvictLast);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_nn = make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_dq = make_idesc_bf16(128, 64, 0, 1);
+      mbar_wait(q_full, 0);
+      for (int j = 0; j < nkv; ++j) {
+        const int st = j & 1;
+        const uint8_t* sK = sKV + st * 2 * kTile;
+        const uint8_t* sV = sK + kTile;
+        mbar_wait(&kv_full[st], (j >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) umma_ss(tS, kdesc(sQ, kk), kdesc(sK, kk), idesc_nn, kk > 0);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) umma_ss(tdP, kdesc(sdO, kk), kdesc(sV, kk), idesc_nn, kk > 0);
+        umma_commit(s_full);
+        mbar_wait(ds_full, j & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_ss(tdQ, kdesc128(sdS, kk), mndesc(sK, kk), idesc_dq, (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&kv_empty[st]);
+        umma_commit(dq_done);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const int iq = qb * 128 + r;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    const float scale_l2 = p.scale * kLog2e;
+    const float slope_l2 = p.alibi != nullptr ? p.alibi[h] * kLog2e : 0.f;
+    const float inv_keep = p.p_drop > 0.f ? 1.f / (1.f - p.p_drop) : 1.f;
+    const float* kb = p.key_bias != nullptr ? p.key_bias + static_cast<size_t>(b) * p.S : nullptr;
+    const float lse = p.lse[static_cast<size_t>(bh) * p.S + iq];
+    const float lse_l2 = lse * kLog2e;
+    const float dlt = p.delta[static_cast<size_t>(bh) * p.S + iq];
+    uint32_t rs[32], rp[32];
+    float v[32];
+    for (int j = 0; j < nkv; ++j) {
+      mbar_wait(s_full, j & 1);
+      tc_fence_after();
+      if (j > 0) {  // dS smem is still being read by the previous dQ MMA
+        mbar_wait(dq_done, (j - 1) & 1);
+        tc_fence_after();
+      }
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        tmem_ld_32x32(tS + lane_off + c * 32, rs);
+        tmem_ld_32x32(tdP + lane_off + c * 32, rp);
+        tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+          const int jk = j * 128 + c * 32 + t;
+          float x = __uint_as_float(rs[t]) * scale_l2;
+          if (p.alibi != nullptr) x += slope_l2 * static_cast<float>(jk - iq);
+          if (kb != nullptr) x += kb[jk] * kLog2e;
+          float pr = exp2f(x - lse_l2);
+          if ((p.causal && jk > iq) || lse == -INFINITY) pr = 0.f;
+          const float dp = __uint_as_float(rp[t]) * attn_keep(p, bh, iq, jk, inv_keep);
+          v[t] = pr * (dp - dlt) * p.scale;
+        }
+        store_chunk_sw128(sdS, r, c * 32, v);
+      }
+      fence_async_shared();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(ds_full);
+    }
+    mbar_wait(dq_done, (nkv - 1) & 1);
+    tc_fence_after();
+    __nv_bfloat16* dst = p.dqkv + static_cast<size_t>(row0 + iq) * (3 * p.H) + h * 64;
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+      tmem_ld_32x32(tdQ + lane_off + c * 32, rs);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        *reinterpret_cast<uint4*>(dst + c * 32 + g * 8) = make_uint4(
+            pack_bf16x2(__uint_as_float(rs[g * 8 + 0]), __uint_as_float(rs[g * 8 + 1])),
+            pack_bf16x2(__uint_as_float(rs[g * 8 + 2]), __uint_as_float(rs[g * 8 + 3])),
+            pack_bf16x2(__uint_as_float(rs[g * 8 + 4]), __uint_as_float(rs[g * 8 + 5])),
+            pack_bf16x2(__uint_as_float(rs[g * 8 + 6]), __uint_as_float(rs[g * 8 + 7])));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// ============================================================================== backward: dK, dV
+__global__ void __launch_bounds__(kAttnThreads)
+attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
+                     const __grid_constant__ CUtensorMap tm_do, const AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* sK = smem;
+  uint8_t* sV = smem + kTile;
+  uint8_t* sQdO = smem + 2 * kTile;  // 2 stages x (Q | dO)
+  uint8_t* sPT = smem + 6 * kTile;   // [128 keys x 128 queries]
+  uint8_t* sdST = smem + 8 * kTile;  // [128 keys x 128 queries]
+  float* sLse = reinterpret_cast<float*>(smem + 10 * kTile);  // [128]
+  float* sDelta = sLse + 128;                                  // [128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDelta + 128);
+  uint64_t* kv_full = bars;
+  uint64_t* q_full = bars + 1;
+  uint64_t* q_empty = bars + 3;
+  uint64_t* st_full = bars + 5;
+  uint64_t* pt_full = bars + 6;
+  uint64_t* acc_done = bars + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  check_smem_alignment(smem);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kb_idx = blockIdx.x, bh = blockIdx.y;
+  const int b = bh / p.heads, h = bh % p.heads;
+  const int row0 = b * p.S;
+  const int nq = p.S / 128;
+  const int i0 = p.causal ? kb_idx : 0;  // first query block that can see these keys
+  const int niter = nq - i0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_do);
+    mbar_init(kv_full, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
+    mbar_init(st_full, 1);
+    mbar_init(pt_full, 4);
+    mbar_init(acc_done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tST = tmem, tdPT = tmem + 128, tdK = tmem + 256, tdV = tmem + 320;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * kTile);
+      tma_load_2d(sK, &tm_qkv, kv_full, p.H + h * 64, row0 + kb_idx * 128, kEvictNormal);
+      tma_load_2d(sV, &tm_qkv, kv_full, 2 * p.H + h * 64, row0 + kb_idx * 128, kEvictNormal);
+      for (int it = 0; it < niter; ++it) {
+        const int st = it & 1, i = i0 + it;
+        mbar_wait(&q_empty[st], ((it >> 1) & 1) ^ 1);
+        mbar_expect_tx(&q_full[st], 2 * kTile);
+        tma_load_2d(sQdO + st * 2 * kTile, &tm_qkv, &q_full[st], h * 64, row0 + i * 128, kEvictLast);
+        tma_load_2d(sQdO + st * 2 * kTile + kTile, &tm_do, &q_full[st], h * 64, row0 + i * 128, kEvictLast);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_nn = make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_acc = make_idesc_bf16(128, 64, 0, 1);
+      mbar_wait(kv_full, 0);
+      for (int it = 0; it < niter; ++it) {
+        const int st = it & 1;
+        const uint8_t* sQ = sQdO + st * 2 * kTile;
+        const uint8_t* sdO = sQ + kTile;
+        mbar_wait(&q_full[st], (it >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) umma_ss(tST, kdesc(sK, kk), kdesc(sQ, kk), idesc_nn, kk > 0);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) umma_ss(tdPT, kdesc(sV, kk), kdesc(sdO, kk), idesc_nn, kk > 0);
+        umma_commit(st_full);
+        mbar_wait(pt_full, it & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_ss(tdV, kdesc128(sPT, kk), mndesc(sdO, kk), idesc_acc, (it > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          umma_ss(tdK, kdesc128(sdST, kk), mndesc(sQ, kk), idesc_acc, (it > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&q_empty[st]);
+        umma_commit(acc_done);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int r = q * 32 + lane;       // key row within the block
+    const int jk = kb_idx * 128 + r;   // absolute key index
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    const float scale_l2 = p.scale * kLog2e;
+    const float slope_l2 = p.alibi != nullptr ? p.alibi[h] * kLog2e : 0.f;
+    const float inv_keep = p.p_drop > 0.f ? 1.f / (1.f - p.p_drop) : 1.f;
+    const float kbias_l2 =
+        p.key_bias != nullptr ? p.key_bias[static_cast<size_t>(b) * p.S + jk] * kLog2e : 0.f;
+    uint32_t rs[32], rp[32];
+    float vp[32], vd[32];
+    for (int it = 0; it < niter; ++it) {
+      const int i = i0 + it;
+      // per-query statistics of this query block -> smem (previous readers are done: they
+      // passed the named barrier at the end of the last iteration)
+      sLse[r] = p.lse[static_cast<size_t>(bh) * p.S + i * 128 + r] * kLog2e;
+      sDelta[r] = p.delta[static_cast<size_t>(bh) * p.S + i * 128 + r];
+      named_bar_sync(1, 128);
+      mbar_wait(st_full, it & 1);
+      tc_fence_after();
+      if (it > 0) {  // sPT / sdST are still being read by the previous accumulation MMAs
+        mbar_wait(acc_done, (it - 1) & 1);
+        tc_fence_after();
+      }
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        tmem_ld_32x32(tST + lane_off + c * 32, rs);
+        tmem_ld_32x32(tdPT + lane_off + c * 32, rp);
+        tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+          const int iq = i * 128 + c * 32 + t;
+          float x = __uint_as_float(rs[t]) * scale_l2 + kbias_l2;
+          if (p.alibi != nullptr) x += slope_l2 * static_cast<float>(jk - iq);
+          const float l2 = sLse[c * 32 + t];
+          float pr = exp2f(x - l2);
+          if ((p.causal && jk > iq) || l2 == -INFINITY) pr = 0.f;
+          const float keep = attn_keep(p, bh, iq, jk, inv_keep);
+          vp[t] = pr * keep;
+          vd[t] = pr * (__uint_as_float(rp[t]) * keep - sDelta[c * 32 + t]) * p.scale;
+        }
+        store_chunk_sw128(sPT, r, c * 32, vp);
+        store_chunk_sw128(sdST, r, c * 32, vd);
+      }
+      fence_async_shared();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pt_full);
+      named_bar_sync(1, 128);  // everyone is done with sLse/sDelta before the next overwrite
+    }
+    mbar_wait(acc_done, (niter - 1) & 1);
+    tc_fence_after();
+    __nv_bfloat16* dk = p.dqkv + static_cast<size_t>(row0 + jk) * (3 * p.H) + p.H + h * 64;
+    __nv_bfloat16* dv = dk + p.H;
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+      tmem_ld_32x32(tdK + lane_off + c * 32, rs);
+      tmem_ld_32x32(tdV + lane_off + c * 32, rp);
+      tmem_ld_wait();
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        *reinterpret_cast<uint4*>(dk + c * 32 + g * 8) = make_uint4(
+            pack_bf16x2(__uint_as_float(rs[g * 8 + 0]), __uint_as_float(rs[g * 8 + 1])),
+            pack_bf16x2(__uint_as_float(rs[g * 8 + 2]), __uint_as_float(rs[g * 8 + 3])),
+            pack_bf16x2(__uint_as_float(rs[g * 8 + 4]), __uint_as_float(rs[g * 8 + 5])),
+            pack_bf16x2(__uint_as_float(rs[g * 8 + 6]), __uint_as_float(rs[g * 8 + 7])));
+        *reinterpret_cast<uint4*>(dv + c * 32 + g * 8) = make_uint4(
+            pack_bf16x2(__uint_as_float(rp[g * 8 + 0]), __uint_as_float(rp[g * 8 + 1])),
+            pack_bf16x2(__uint_as_float(rp[g * 8 + 2]), __uint_as_float(rp[g * 8 + 3])),
+            pack_bf16x2(__uint_as_float(rp[g * 8 + 4]), __uint_as_float(rp[g * 8 + 5])),
+            pack_bf16x2(__uint_as_float(rp[g * 8 + 6]), __uint_as_float(rp[g * 8 + 7])));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+constexpr int kFwdSmem = 7 * kTile + 128;
+constexpr int kDqSmem = 8 * kTile + 128;
+constexpr int kDkdvSmem = 10 * kTile + 1024 + 128;
+
+static int check_attn_args(int B, int S, int heads, int head_dim, int ld_qkv) {
+  if (head_dim != 64 || S % 128 != 0 || B <= 0 || heads <= 0 || ld_qkv % 8 != 0) {
+    fprintf(stderr,
+            "[dtds] fused attention needs head_dim == 64 and seq %% 128 == 0 (got head_dim=%d "
+            "seq=%d); use the unfused module path for other shapes\n",
+            head_dim, S);
+    return -1;
+  }
+  return 0;
+}
+
+}  // namespace dtds
+
+using namespace dtds;
+
+extern "C" int dtds_attention_fwd(const void* qkv, int ld_qkv, void* out, float* lse,
+                                  const float* key_bias, const float* alibi_slopes, int B, int S,
+                                  int heads, int head_dim, float scale, int causal, float p_drop,
+                                  unsigned long long seed, cudaStream_t stream) {
+  if (check_attn_args(B, S, heads, head_dim, ld_qkv)) return -1;
+  const int H = heads * 64;
+  CUtensorMap tm;
+  int rc = make_tmap_2d_bf16(&tm, qkv, 3 * H, static_cast<uint64_t>(B) * S, ld_qkv, 64, 128);
+  if (rc) return rc;
+  AttnParams p{};
+  p.B = B; p.S = S; p.heads = heads; p.H = H; p.scale = scale; p.causal = causal;
+  p.key_bias = key_bias; p.alibi = alibi_slopes; p.p_drop = p_drop; p.seed = seed;
+  p.out = static_cast<__nv_bfloat16*>(out); p.lse = lse;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+    attr_set = true;
+  }
+  dim3 grid(S / 128, B * heads);
+  attn_fwd_kernel<<<grid, kAttnThreads, kFwdSmem, stream>>>(tm, p);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtds_attention_bwd(const void* qkv, int ld_qkv, const void* out, const void* dout,
+                                  const float* lse, float* delta, void* dqkv, const float* key_bias,
+                                  const float* alibi_slopes, int B, int S, int heads, int head_dim,
+                                  float scale, int causal, float p_drop, unsigned long long seed,
+                                  cudaStream_t stream) {
+  if (check_attn_args(B, S, heads, head_dim, ld_qkv)) return -1;
+  const int H = heads * 64;
+  CUtensorMap tm, tmdo;
+  int rc = make_tmap_2d_bf16(&tm, qkv, 3 * H, static_cast<uint64_t>(B) * S, ld_qkv, 64, 128);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tmdo, dout, H, static_cast<uint64_t>(B) * S, H, 64, 128);
+  if (rc) return rc;
+  AttnParams p{};
+  p.B = B; p.S = S; p.heads = heads; p.H = H; p.scale = scale; p.causal = causal;
+  p.key_bias = key_bias; p.alibi = alibi_slopes; p.p_drop = p_drop; p.seed = seed;
+  p.lse = const_cast<float*>(lse); p.delta = delta; p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
+  static bool attr_set = false;
+  if (!attr_set) {
+    DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDqSmem));
+    DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDkdvSmem));
+    attr_set = true;
+  }
+  attn_delta_kernel<<<(B * S + 7) / 8, 256, 0, stream>>>(
+      static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, B, S, heads);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  dim3 grid(S / 128, B * heads);
+  attn_bwd_dkdv_kernel<<<grid, kAttnThreads, kDkdvSmem, stream>>>(tm, tmdo, p);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  attn_bwd_dq_kernel<<<grid, kAttnThreads, kDqSmem, stream>>>(tm, tmdo, p);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,489 @@
+// tcgen05 / TMEM / TMA GEMM family for sm_100a (bf16 operands, fp32 accumulation).
+//
+//   D[M,N] = epilogue( alpha * sum_k A[m,k] * B[n,k] )
+//
+// Operands may be K-major (the contraction index is contiguous in memory) or MN-major (the
+// output index is contiguous), which covers forward (x·Wᵀ), dgrad (dy·W) and wgrad (dyᵀ·x)
+// without transposing anything in memory.  Replaces the cuBLAS SGEMM calls behind every
+// nn.Linear in the reference (model/transformer.py:37-40,50-51; HF BertLayer in
+// model/bert_mp.py:22-24) — SURVEY.md rows K1/K2.
+//
+// Structure: persistent kernel, one CTA per SM, 6 warps:
+//   warp 0      TMA producer    (cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx)
+//   warp 1      MMA issuer      (one thread issues tcgen05.mma, accumulators in TMEM, 2 stages)
+//   warps 2..5  epilogue        (tcgen05.ld -> bias / activation / residual -> global)
+// The epilogue of tile i overlaps the main loop of tile i+1 through the double-buffered TMEM
+// accumulator.  When `peer_flags` is given (ZeRO-3 all-gather fused GEMM) the producer waits on
+// the per-chunk arrival flag of the B rows it is about to load; see fused_comm.cu.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "common.cuh"
+#include "dtds_b200.h"
+#include "internal.h"
+
+namespace dtds {
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;
+constexpr int kGemmThreads = 192;
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kAStage = kBM * kBK * 2;
+  static constexpr int kBStage = BN * kBK * 2;
+  static constexpr int kStage = kAStage + kBStage;
+  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kTmemCols = 2 * BN;  // two accumulator stages
+  static constexpr int kSmemBytes = kStages * kStage + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct GemmParams {
+  void* D;
+  const __nv_bfloat16* bias;      // [N] or null
+  const __nv_bfloat16* residual;  // [M, ld_res] or null, added after the activation
+  __nv_bfloat16* pre_out;         // [M, ldd] or null: pre-activation values kept for backward
+  const __nv_bfloat16* dact_in;   // [M, ld_dact] or null: multiply result by act'(dact_in)
+  const uint32_t* ready_flags;    // null, or per-B-chunk arrival flags (all-gather fused mode)
+  uint32_t ready_epoch;           // value a flag must reach before its chunk may be read
+  int rows_per_flag;              // B rows (n index) covered by one flag
+  int M, N, K;
+  int ldd, ld_res, ld_dact;
+  int act;
+  int out_fp32;
+  int accumulate;  // D += result
+  float alpha;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + Cfg::kStages * Cfg::kAStage;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStage);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + Cfg::kStages;
+  uint64_t* tmem_full = bars + 2 * Cfg::kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int num_m = (p.M + kBM - 1) / kBM;
+  const int num_n = (p.N + BN - 1) / BN;
+  const int num_tiles = num_m * num_n;
+  const int num_kb = (p.K + kBK - 1) / kBK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile % num_m) * kBM;
+        const int n0 = (tile / num_m) * BN;
+        if (p.ready_flags != nullptr) {
+          // All-gather fused mode: B rows [n0, n0+BN) were written by copy CTAs (possibly of
+          // another kernel on a side stream); wait for the arrival flag(s) covering them, then
+          // order the generic-proxy writes before our async-proxy (TMA) reads.
+          const int f0 = n0 / p.rows_per_flag;
+          const int n_last = min(n0 + BN, p.N) - 1;
+          const int f1 = n_last / p.rows_per_flag;
+          for (int f = f0; f <= f1; ++f) {
+            uint32_t spins = 0, v;
+            do {
+              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p.ready_flags + f));
+              if (++spins > DTDS_SPIN_LIMIT) {
+                printf("[dtds] gemm: ready flag %d stuck at %u (want %u)\n", f, v, p.ready_epoch);
+                __trap();
+              }
+            } while (v < p.ready_epoch);
+          }
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty[s], ph ^ 1);
+          mbar_expect_tx(&full[s], Cfg::kStage);
+          uint8_t* a_dst = sA + s * Cfg::kAStage;
+          uint8_t* b_dst = sB + s * Cfg::kBStage;
+          if constexpr (!A_MN) {
+            tma_load_2d(a_dst, &tmA, &full[s], kb * kBK, m0, kEvictNormal);
+          } else {
+#pragma unroll
+            for (int j = 0; j < kBM / 64; ++j)
+              tma_load_2d(a_dst + j * 8192, &tmA, &full[s], m0 + j * 64, kb * kBK, kEvictNormal);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d(b_dst, &tmB, &full[s], kb * kBK, n0, kEvictNormal);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(b_dst + j * 8192, &tmB, &full[s], n0 + j * 64, kb * kBK, kEvictNormal);
+          }
+          if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(kBM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      int s = 0;
+      uint32_t ph = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const int as = it & 1;
+        const uint32_t aph = (it >> 1) & 1;
+        mbar_wait(&tmem_empty[as], aph ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + s * Cfg::kAStage);
+          const uint32_t b_addr = smem_u32(sB + s * Cfg::kBStage);
+#pragma unroll
+          for (int kk = 0; kk < kBK / 16; ++kk) {
+            const uint64_t adesc = A_MN ? make_smem_desc_sw128(a_addr + kk * 2048, 8192, 1024)
+                                        : make_smem_desc_sw128(a_addr + kk * 32, 16, 1024);
+            const uint64_t bdesc = B_MN ? make_smem_desc_sw128(b_addr + kk * 2048, 8192, 1024)
+                                        : make_smem_desc_sw128(b_addr + kk * 32, 16, 1024);
+            umma_ss(d_tmem, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty[s]);  // frees the smem slot once these MMAs have read it
+          if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
+        }
+        umma_commit(&tmem_full[as]);  // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps
+    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int m0 = (tile % num_m) * kBM;
+      const int n0 = (tile / num_m) * BN;
+      const int as = it & 1;
+      const uint32_t aph = (it >> 1) & 1;
+      mbar_wait(&tmem_full[as], aph);
+      tc_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = n0 + c * 32;
+        if (col0 >= p.N) break;  // warp-uniform
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c * 32, r);
+        tmem_ld_wait();
+        if (!row_ok) continue;
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+        const bool full_chunk = (col0 + 32 <= p.N);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (full_chunk || col0 + j < p.N) v[j] += __bfloat162float(__ldg(p.bias + col0 + j));
+        }
+        if (p.pre_out != nullptr) {
+          __nv_bfloat16* dst = p.pre_out + static_cast<size_t>(row) * p.ldd + col0;
+          if (full_chunk) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 o = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
+                                   pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
+              *reinterpret_cast<uint4*>(dst + j) = o;
+            }
+          } else {
+            for (int j = 0; j < 32 && col0 + j < p.N; ++j) dst[j] = __float2bfloat16(v[j]);
+          }
+        }
+        if (p.act != ACT_NONE && p.dact_in == nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act);
+        }
+        if (p.dact_in != nullptr) {
+          const __nv_bfloat16* src = p.dact_in + static_cast<size_t>(row) * p.ld_dact + col0;
+          if (full_chunk) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              const uint4 u = *reinterpret_cast<const uint4*>(src + j);
+              const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                v[j + 2 * t] *= act_grad(bf16_lo(w[t]), p.act);
+                v[j + 2 * t + 1] *= act_grad(bf16_hi(w[t]), p.act);
+              }
+            }
+          } else {
+            for (int j = 0; j < 32 && col0 + j < p.N; ++j)
+              v[j] *= act_grad(__bfloat162float(src[j]), p.act);
+          }
+        }
+        if (p.residual != nullptr) {
+          const __nv_bfloat16* src = p.residual + static_cast<size_t>(row) * p.ld_res + col0;
+          if (full_chunk) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              const uint4 u = *reinterpret_cast<const uint4*>(src + j);
+              const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                v[j + 2 * t] += bf16_lo(w[t]);
+                v[j + 2 * t + 1] += bf16_hi(w[t]);
+              }
+            }
+          } else {
+            for (int j = 0; j < 32 && col0 + j < p.N; ++j) v[j] += __bfloat162float(src[j]);
+          }
+        }
+        if (p.out_fp32) {
+          float* dst = reinterpret_cast<float*>(p.D) + static_cast<size_t>(row) * p.ldd + col0;
+          if (full_chunk) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              if (p.accumulate) {
+                const float4 old = *reinterpret_cast<const float4*>(dst + j);
+                o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+              }
+              *reinterpret_cast<float4*>(dst + j) = o;
+            }
+          } else {
+            for (int j = 0; j < 32 && col0 + j < p.N; ++j)
+              dst[j] = p.accumulate ? dst[j] + v[j] : v[j];
+          }
+        } else {
+          __nv_bfloat16* dst =
+              reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<size_t>(row) * p.ldd + col0;
+          if (full_chunk) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              if (p.accumulate) {
+                const uint4 u = *reinterpret_cast<const uint4*>(dst + j);
+                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                  v[j + 2 * t] += bf16_lo(w[t]);
+                  v[j + 2 * t + 1] += bf16_hi(w[t]);
+                }
+              }
+              uint4 o = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
+                                   pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
+              *reinterpret_cast<uint4*>(dst + j) = o;
+            }
+          } else {
+            for (int j = 0; j < 32 && col0 + j < p.N; ++j) {
+              const float o = p.accumulate ? v[j] + __bfloat162float(dst[j]) : v[j];
+              dst[j] = __float2bfloat16(o);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+// ---------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// Builds a 2-D bf16 tensor map with 128B swizzle.  dim0 is the contiguous dimension.
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1,
+                      uint64_t ld_elems, uint32_t box0, uint32_t box1) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) {
+    fprintf(stderr, "[dtds] cuTensorMapEncodeTiled entry point not available\n");
+    return -1;
+  }
+  cuuint64_t dims[2] = {dim0, dim1};
+  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint32_t box[2] = {box0, box1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr,
+            "[dtds] cuTensorMapEncodeTiled failed (%d): base=%p dims=(%llu,%llu) ld=%llu "
+            "box=(%u,%u)\n",
+            (int)r, base, (unsigned long long)dim0, (unsigned long long)dim1,
+            (unsigned long long)ld_elems, box0, box1);
+    return -2;
+  }
+  return 0;
+}
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (cached[dev] == 0) {
+    int n = 0;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    cached[dev] = n > 0 ? n : 148;
+  }
+  return cached[dev];
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
+                       int max_ctas, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    DTDS_HOST_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Cfg::kSmemBytes));
+    attr_set[dev & 63] = true;
+  }
+  const int num_tiles = ((p.M + kBM - 1) / kBM) * ((p.N + BN - 1) / BN);
+  int grid = sm_count();
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (num_tiles < grid) grid = num_tiles;
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, p);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  return 0;
+}
+
+static int pick_block_n(int M, int N, int requested) {
+  if (requested == 64 || requested == 128 || requested == 256) return requested;
+  const int sms = sm_count();
+  const int num_m = (M + kBM - 1) / kBM;
+  // Largest tile that still gives every SM at least one tile; otherwise the smallest tile.
+  const int cands[3] = {256, 128, 64};
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cands[i];
+    if (bn > 64 && N < bn) continue;
+    const int tiles = num_m * ((N + bn - 1) / bn);
+    if (tiles >= sms) return bn;
+  }
+  return 64;
+}
+
+}  // namespace dtds
+
+using namespace dtds;
+
+extern "C" int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const void* bias,
+                                 const void* residual, void* pre_out, const void* dact_in, int M,
+                                 int N, int K, int lda, int ldb, int ldd, int ld_res, int ld_dact,
+                                 int a_mn_major, int b_mn_major, int act, int out_fp32,
+                                 int accumulate, float alpha, int block_n, int max_ctas,
+                                 const void* ready_flags, unsigned ready_epoch, int rows_per_flag,
+                                 cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) ||
+      (reinterpret_cast<uintptr_t>(D) & 15) || (lda % 8) || (ldb % 8) ||
+      (ldd % (out_fp32 ? 4 : 8))) {
+    fprintf(stderr,
+            "[dtds] gemm: operands must be 16-byte aligned with leading dimensions that are "
+            "multiples of 8 elements (lda=%d ldb=%d ldd=%d)\n",
+            lda, ldb, ldd);
+    return -3;
+  }
+  const int bn = pick_block_n(M, N, block_n);
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!a_mn_major) rc = make_tmap_2d_bf16(&tmA, A, K, M, lda, kBK, kBM);
+  else             rc = make_tmap_2d_bf16(&tmA, A, M, K, lda, 64, kBK);
+  if (rc) return rc;
+  if (!b_mn_major) rc = make_tmap_2d_bf16(&tmB, B, K, N, ldb, kBK, bn);
+  else             rc = make_tmap_2d_bf16(&tmB, B, N, K, ldb, 64, kBK);
+  if (rc) return rc;
+
+  GemmParams p;
+  p.D = D;
+  p.bias = static_cast<const __nv_bfloat16*>(bias);
+  p.residual = static_cast<const __nv_bfloat16*>(residual);
+  p.pre_out = static_cast<__nv_bfloat16*>(pre_out);
+  p.dact_in = static_cast<const __nv_bfloat16*>(dact_in);
+  p.ready_flags = static_cast<const uint32_t*>(ready_flags);
+  p.ready_epoch = ready_epoch;
+  p.rows_per_flag = rows_per_flag > 0 ? rows_per_flag : N;
+  p.M = M; p.N = N; p.K = K;
+  p.ldd = ldd; p.ld_res = ld_res > 0 ? ld_res : ldd; p.ld_dact = ld_dact > 0 ? ld_dact : ldd;
+  p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate; p.alpha = alpha;
+
+#define DTDS_DISPATCH(BN_)                                                                     \
+  if (bn == BN_) {                                                                             \
+    if (!a_mn_major && !b_mn_major) return launch_gemm<BN_, false, false>(tmA, tmB, p, max_ctas, stream); \
+    if (!a_mn_major && b_mn_major)  return launch_gemm<BN_, false, true>(tmA, tmB, p, max_ctas, stream);  \
+    if (a_mn_major && !b_mn_major)  return launch_gemm<BN_, true, false>(tmA, tmB, p, max_ctas, stream);  \
+    return launch_gemm<BN_, true, true>(tmA, tmB, p, max_ctas, stream);                        \
+  }
+  DTDS_DISPATCH(64)
+  DTDS_DISPATCH(128)
+  DTDS_DISPATCH(256)
+#undef DTDS_DISPATCH
+  return -4;
+}
+
+extern "C" int dtds_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N,
+                              int K, int lda, int ldb, int ldd, int a_mn_major, int b_mn_major,
+                              int act, int out_fp32, cudaStream_t stream) {
+  return dtds_gemm_bf16_ex(A, B, D, bias, nullptr, nullptr, nullptr, M, N, K, lda, ldb, ldd, 0, 0,
+                           a_mn_major, b_mn_major, act, out_fp32, 0, 1.0f, 0, 0, nullptr, 0, 0,
+                           stream);
+}

@@ -1,0 +1,407 @@
+"""Raw (non-autograd) op entry points.
+
+Each function takes tensors, dispatches CUDA tensors to the hand-written sm_100a kernel through
+the C ABI (mandatory on a GPU machine — no eager fallback) and CPU tensors to ``reference.py``.
+Shapes follow the C header ``include/dtds_b200.h``.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib, reference as ref
+from .reference import ACT_NONE
+
+_scratch: dict = {}
+
+
+def _scratch_f32(device, n: int, tag: str, zero: bool = False) -> torch.Tensor:
+    key = (device, tag)
+    t = _scratch.get(key)
+    if t is None or t.numel() < n:
+        t = torch.zeros(max(n, 1024), dtype=torch.float32, device=device)
+        _scratch[key] = t
+    elif zero:
+        t[:n].zero_()
+    return t
+
+
+def _c(t: torch.Tensor) -> torch.Tensor:
+    return t if t.is_contiguous() else t.contiguous()
+
+
+# --------------------------------------------------------------------------------------- GEMM
+def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, residual=None,
+         pre_out=None, dact_in=None, alpha=1.0, out=None, out_dtype=None, accumulate=False,
+         block_n=0, max_ctas=0, ready_flags=None, ready_epoch=0, rows_per_flag=0):
+    """D[M,N] = act(alpha * A·Bᵀ + bias) (+ residual).
+
+    a: [M,K] (or [K,M] when a_mn_major); b: [N,K] (or [K,N] when b_mn_major).  2-D tensors whose
+    last dimension is contiguous; row strides must be multiples of 8 elements.
+    """
+    if a_mn_major:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_mn_major:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    assert K == Kb, f"contraction mismatch {K} vs {Kb}"
+    if not _lib.use_native(a, b):
+        acc_into = out if accumulate else None
+        res = ref.gemm(a, b, a_mn_major=a_mn_major, b_mn_major=b_mn_major, bias=bias, act=act,
+                       residual=residual, dact_in=dact_in, alpha=alpha,
+                       out_dtype=out_dtype or (out.dtype if out is not None else a.dtype),
+                       accumulate_into=acc_into, want_pre=pre_out is not None)
+        if pre_out is not None:
+            res, pre = res
+            pre_out.copy_(pre)
+        if out is not None:
+            out.copy_(res)
+            return out
+        return res
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "native GEMM operands are bf16"
+    assert a.stride(-1) == 1 and b.stride(-1) == 1
+    if out is None:
+        out = torch.empty(M, N, dtype=out_dtype or torch.bfloat16, device=a.device)
+    assert out.stride(-1) == 1 and out.shape == (M, N)
+    out_fp32 = out.dtype == torch.float32
+    L = _lib.lib()
+    rc = L.dtds_gemm_bf16_ex(
+        a.data_ptr(), b.data_ptr(), out.data_ptr(), _lib.ptr(bias), _lib.ptr(residual),
+        _lib.ptr(pre_out), _lib.ptr(dact_in), M, N, K, a.stride(0), b.stride(0), out.stride(0),
+        residual.stride(0) if residual is not None else 0,
+        dact_in.stride(0) if dact_in is not None else 0,
+        int(a_mn_major), int(b_mn_major), int(act), int(out_fp32), int(accumulate), float(alpha),
+        int(block_n), int(max_ctas), _lib.ptr(ready_flags), int(ready_epoch), int(rows_per_flag),
+        _lib.stream_ptr())
+    _lib.check(rc, "dtds_gemm_bf16_ex")
+    return out
+
+
+# ---------------------------------------------------------------------------------- LayerNorm
+def layernorm_fwd(x, residual, gamma, beta, eps, p_drop=0.0, seed=0, save_z=True):
+    """Returns (y, z, mean, rstd); z = dropout(x) + residual is what backward needs."""
+    cols = x.shape[-1]
+    rows = x.numel() // cols
+    if not _lib.use_native(x):
+        return ref.layernorm_fwd(x, residual, gamma, beta, eps, p_drop, seed)
+    x = _c(x)
+    y = torch.empty_like(x)
+    need_z = save_z and (residual is not None or p_drop > 0.0)
+    z = torch.empty_like(x) if need_z else None
+    mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+    rc = _lib.lib().dtds_layernorm_fwd(
+        x.data_ptr(), _lib.ptr(_c(residual) if residual is not None else None), gamma.data_ptr(),
+        beta.data_ptr(), y.data_ptr(), _lib.ptr(z), mean.data_ptr(), rstd.data_ptr(), rows, cols,
+        float(eps), float(p_drop), int(seed), _lib.stream_ptr())
+    _lib.check(rc, "dtds_layernorm_fwd")
+    return y, (z if need_z else x), mean, rstd
+
+
+def layernorm_bwd(dy, z, mean, rstd, gamma, dz_extra=None, p_drop=0.0, seed=0, dgamma_out=None,
+                  dbeta_out=None, accumulate=False, want_dx_drop=False):
+    """Returns (dz, dx_drop, dgamma, dbeta).  dgamma/dbeta are written into *_out if given."""
+    cols = z.shape[-1]
+    rows = z.numel() // cols
+    if not _lib.use_native(dy):
+        dz, dxd, dg, db = ref.layernorm_bwd(dy, z, mean, rstd, gamma, dz_extra, p_drop, seed)
+        dz, dxd = dz.to(dy.dtype), dxd.to(dy.dtype)
+        if dgamma_out is not None:
+            if accumulate:
+                dgamma_out.add_(dg.to(dgamma_out.dtype)); dbeta_out.add_(db.to(dbeta_out.dtype))
+            else:
+                dgamma_out.copy_(dg); dbeta_out.copy_(db)
+            dg, db = dgamma_out, dbeta_out
+        else:
+            dg, db = dg.to(gamma.dtype), db.to(gamma.dtype)
+        return dz, (dxd if want_dx_drop else None), dg, db
+    dy, z = _c(dy), _c(z)
+    dz = torch.empty_like(dy)
+    dxd = torch.empty_like(dy) if (want_dx_drop and p_drop > 0.0) else None
+    if dgamma_out is None:
+        dgamma_out = torch.empty_like(gamma)
+        dbeta_out = torch.empty_like(gamma)
+        accumulate = False
+    L = _lib.lib()
+    blocks = L.dtds_layernorm_bwd_blocks(rows, cols)
+    partial = _scratch_f32(dy.device, blocks * 2 * cols, "ln_partial")
+    rc = L.dtds_layernorm_bwd(
+        dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
+        _lib.ptr(_c(dz_extra) if dz_extra is not None else None), dz.data_ptr(), _lib.ptr(dxd),
+        dgamma_out.data_ptr(), dbeta_out.data_ptr(), partial.data_ptr(), rows, cols, float(p_drop),
+        int(seed), int(dgamma_out.dtype == torch.float32), int(accumulate), _lib.stream_ptr())
+    _lib.check(rc, "dtds_layernorm_bwd")
+    if want_dx_drop and dxd is None:
+        dxd = dz
+    return dz, dxd, dgamma_out, dbeta_out
+
+
+def colsum(x, out=None, accumulate=False):
+    """out[c] = sum_r x[r, c] for a 2-D bf16 matrix (bias gradients)."""
+    rows, cols = x.shape
+    if not _lib.use_native(x):
+        s = x.float().sum(0)
+        if out is None:
+            return s.to(x.dtype)
+        if accumulate:
+            out.add_(s.to(out.dtype))
+        else:
+            out.copy_(s)
+        return out
+    assert x.stride(1) == 1
+    if out is None:
+        out = torch.empty(cols, dtype=x.dtype, device=x.device)
+        accumulate = False
+    scratch = _scratch_f32(x.device, cols, "colsum")  # kernel leaves it zeroed after use
+    rc = _lib.lib().dtds_colsum(x.data_ptr(), rows, cols, x.stride(0), scratch.data_ptr(),
+                                out.data_ptr(), int(out.dtype == torch.float32), int(accumulate),
+                                _lib.stream_ptr())
+    _lib.check(rc, "dtds_colsum")
+    return out
+
+
+# -------------------------------------------------------------------------------- elementwise
+def act_fwd(x, act):
+    if not _lib.use_native(x):
+        return ref.act_fwd(x.float(), act).to(x.dtype)
+    x = _c(x)
+    y = torch.empty_like(x)
+    _lib.check(_lib.lib().dtds_act_fwd(x.data_ptr(), y.data_ptr(), x.numel(), int(act),
+                                       _lib.stream_ptr()), "dtds_act_fwd")
+    return y
+
+
+def act_bwd(dy, x, act):
+    if not _lib.use_native(x):
+        return (dy.float() * ref.act_grad(x, act)).to(dy.dtype)
+    x, dy = _c(x), _c(dy)
+    dx = torch.empty_like(x)
+    _lib.check(_lib.lib().dtds_act_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), x.numel(),
+                                       int(act), _lib.stream_ptr()), "dtds_act_bwd")
+    return dx
+
+
+def dropout(x, p, seed, residual=None):
+    """y = x * keep_scale(seed, index) (+ residual).  The same call is its own backward."""
+    if not _lib.use_native(x):
+        y = x.float() * ref.dropout_mask_scale(x.shape, p, seed, x.device)
+        if residual is not None:
+            y = y + residual.float()
+        return y.to(x.dtype)
+    x = _c(x)
+    y = torch.empty_like(x)
+    _lib.check(_lib.lib().dtds_dropout(x.data_ptr(), _lib.ptr(_c(residual) if residual is not None else None),
+                                       y.data_ptr(), x.numel(), float(p), int(seed),
+                                       _lib.stream_ptr()), "dtds_dropout")
+    return y
+
+
+def softmax_rows(x):
+    cols = x.shape[-1]
+    if not _lib.use_native(x):
+        return torch.softmax(x.float(), -1).to(x.dtype)
+    x = _c(x)
+    y = torch.empty_like(x)
+    _lib.check(_lib.lib().dtds_softmax_rows(x.data_ptr(), None, y.data_ptr(), x.numel() // cols, cols,
+                                            _lib.stream_ptr()), "dtds_softmax_rows")
+    return y
+
+
+def softmax_rows_bwd(y, dy):
+    cols = y.shape[-1]
+    if not _lib.use_native(y):
+        yf, df = y.float(), dy.float()
+        return (yf * (df - (yf * df).sum(-1, keepdim=True))).to(y.dtype)
+    y, dy = _c(y), _c(dy)
+    dx = torch.empty_like(y)
+    _lib.check(_lib.lib().dtds_softmax_rows(y.data_ptr(), dy.data_ptr(), dx.data_ptr(),
+                                            y.numel() // cols, cols, _lib.stream_ptr()),
+               "dtds_softmax_rows")
+    return dx
+
+
+def mse(x, target, want_grad=True, gscale=1.0):
+    """Returns (loss scalar fp32 tensor, dx or None)."""
+    if not _lib.use_native(x):
+        d = x.float() - target.float()
+        loss = (d * d).mean()
+        dx = (2.0 * d / d.numel() * gscale).to(x.dtype) if want_grad else None
+        return loss, dx
+    x, target = _c(x), _c(target)
+    loss = torch.zeros((), dtype=torch.float32, device=x.device)
+    dx = torch.empty_like(x) if want_grad else None
+    _lib.check(_lib.lib().dtds_mse(x.data_ptr(), target.data_ptr(), _lib.ptr(dx), loss.data_ptr(),
+                                   x.numel(), float(gscale), _lib.stream_ptr()), "dtds_mse")
+    return loss, dx
+
+
+# ------------------------------------------------------------------- embedding / CE / Adam
+def embedding_fwd(ids, word, pos=None, type_emb=None, type_ids=None, pos_offset=0):
+    """ids [B,S] int64 -> [B,S,H]: word[ids] + pos[s + pos_offset] + type[type_ids or 0]."""
+    B, S = ids.shape
+    H = word.shape[1]
+    if not _lib.use_native(word):
+        out = word[ids].float()
+        if pos is not None:
+            out = out + pos[torch.arange(S, device=ids.device) + pos_offset].float()[None]
+        if type_emb is not None:
+            tid = type_ids if type_ids is not None else torch.zeros_like(ids)
+            out = out + type_emb[tid].float()
+        return out.to(word.dtype)
+    ids = _c(ids)
+    out = torch.empty(B, S, H, dtype=word.dtype, device=word.device)
+    rc = _lib.lib().dtds_embedding_fwd(
+        ids.data_ptr(), _lib.ptr(_c(type_ids) if type_ids is not None else None), word.data_ptr(),
+        _lib.ptr(pos), _lib.ptr(type_emb), out.data_ptr(), B * S, S, H, int(pos_offset),
+        word.shape[0], _lib.stream_ptr())
+    _lib.check(rc, "dtds_embedding_fwd")
+    return out
+
+
+def embedding_bwd(ids, dout, dword, dpos=None, pos_offset=0, accumulate_pos=False):
+    """Scatter-adds dout [B,S,H] into dword (atomics, accumulating) and reduces dpos over batch."""
+    B, S = ids.shape
+    H = dout.shape[-1]
+    if not _lib.use_native(dout):
+        if dword is not None:
+            dword.index_add_(0, ids.reshape(-1), dout.reshape(-1, H).to(dword.dtype))
+        if dpos is not None:
+            s = dout.float().sum(0).to(dpos.dtype)
+            if accumulate_pos:
+                dpos[pos_offset:pos_offset + S] += s
+            else:
+                dpos[pos_offset:pos_offset + S] = s
+        return
+    dout, ids = _c(dout), _c(ids)
+    fp32 = (dword if dword is not None else dpos).dtype == torch.float32
+    rc = _lib.lib().dtds_embedding_bwd(
+        ids.data_ptr(), dout.data_ptr(), _lib.ptr(dword), _lib.ptr(dpos), B, S, H, int(pos_offset),
+        dword.shape[0] if dword is not None else 0, int(fp32), int(accumulate_pos),
+        _lib.stream_ptr())
+    _lib.check(rc, "dtds_embedding_bwd")
+
+
+def cross_entropy(logits, labels, *, vocab=None, ignore_index=-100, shift=False, seq=None,
+                  want_grad=True, inplace_grad=True, gscale=1.0):
+    """Mean CE over non-ignored rows of logits [R, ld] (first `vocab` columns are real).
+
+    Returns (loss scalar fp32, dlogits or None).  With inplace_grad the gradient overwrites the
+    logits buffer (the logits are dead after the loss anyway)."""
+    R, ld = logits.shape
+    vocab = vocab or ld
+    seq = seq or R
+    if not _lib.use_native(logits):
+        lf = logits[:, :vocab].float().detach().requires_grad_(want_grad)
+        loss, _ = ref.cross_entropy(lf, labels.reshape(-1), ignore_index=ignore_index, shift=shift,
+                                    seq=seq)
+        if not want_grad:
+            return loss.detach(), None
+        (g,) = torch.autograd.grad(loss, lf)
+        d = torch.zeros_like(logits)
+        d[:, :vocab] = (g * gscale).to(logits.dtype)
+        return loss.detach(), d
+    assert logits.stride(1) == 1 and logits.stride(0) == ld
+    labels = _c(labels.reshape(-1))
+    stats = torch.empty(2, dtype=torch.float32, device=logits.device)
+    d = None
+    if want_grad:
+        d = logits if inplace_grad else torch.empty_like(logits)
+    rc = _lib.lib().dtds_cross_entropy(
+        logits.data_ptr(), labels.data_ptr(), _lib.ptr(d), stats.data_ptr(), None, R, vocab, ld,
+        seq, int(shift), int(ignore_index), float(gscale), _lib.stream_ptr())
+    _lib.check(rc, "dtds_cross_entropy")
+    return stats[1], d
+
+
+def adam_flat(p, g, m, v, step, *, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0,
+              adamw_mode=True, bias_correction=True, grad_scale=1.0, p_lp=None, inc_step=True):
+    """Fused Adam over flat fp32 master weights `p` with state m, v; optional bf16 copy `p_lp`.
+    `step` is an int32 device tensor holding the number of steps already taken."""
+    if not _lib.use_native(p):
+        t = int(step.item()) + 1
+        ref.adam_step(p, g, m, v, t, lr=lr, beta1=beta1, beta2=beta2, eps=eps,
+                      weight_decay=weight_decay, adamw_mode=adamw_mode,
+                      bias_correction=bias_correction, grad_scale=grad_scale)
+        if p_lp is not None:
+            p_lp.copy_(p)
+        if inc_step:
+            step += 1
+        return
+    assert p.dtype == torch.float32 and m.dtype == torch.float32 and v.dtype == torch.float32
+    assert step.dtype == torch.int32
+    rc = _lib.lib().dtds_adam_flat(
+        p.data_ptr(), _lib.ptr(p_lp), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(),
+        step.data_ptr(), int(inc_step), int(g.dtype == torch.float32), float(lr), float(beta1),
+        float(beta2), float(eps), float(weight_decay), float(grad_scale), int(adamw_mode),
+        int(bias_correction), _lib.stream_ptr())
+    _lib.check(rc, "dtds_adam_flat")
+
+
+def cast(src, dst):
+    """Flat fp32<->bf16 cast between preallocated buffers."""
+    if not _lib.use_native(src):
+        dst.copy_(src)
+        return dst
+    to_bf16 = dst.dtype == torch.bfloat16
+    _lib.check(_lib.lib().dtds_cast(src.data_ptr(), dst.data_ptr(), src.numel(), int(to_bf16),
+                                    _lib.stream_ptr()), "dtds_cast")
+    return dst
+
+
+# --------------------------------------------------------------------------------- attention
+def _split_qkv(qkv, B, S, heads):
+    H = qkv.shape[1] // 3
+    d = H // heads
+    q, k, v = qkv.view(B, S, 3, heads, d).unbind(2)  # each [B, S, heads, d]
+    return q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2)
+
+
+def fused_attention_supported(S: int, head_dim: int) -> bool:
+    return head_dim == 64 and S % 128 == 0
+
+
+def attention_fwd(qkv, B, S, heads, *, scale, causal=False, key_bias=None, alibi=None, p_drop=0.0,
+                  seed=0):
+    """qkv [B*S, 3H] (columns Q|K|V, heads*d each) -> (ctx [B*S, H], lse [B, heads, S] fp32)."""
+    H = qkv.shape[1] // 3
+    d = H // heads
+    if not _lib.use_native(qkv):
+        q, k, v = _split_qkv(qkv, B, S, heads)
+        out, lse = ref.attention(q, k, v, scale=scale, causal=causal, key_bias=key_bias,
+                                 alibi_slopes=alibi, p_drop=p_drop, seed=seed)
+        return out.transpose(1, 2).reshape(B * S, H).to(qkv.dtype), lse
+    assert qkv.dtype == torch.bfloat16 and qkv.stride(1) == 1
+    out = torch.empty(B * S, H, dtype=qkv.dtype, device=qkv.device)
+    lse = torch.empty(B, heads, S, dtype=torch.float32, device=qkv.device)
+    rc = _lib.lib().dtds_attention_fwd(
+        qkv.data_ptr(), qkv.stride(0), out.data_ptr(), lse.data_ptr(), _lib.ptr(key_bias),
+        _lib.ptr(alibi), B, S, heads, d, float(scale), int(causal), float(p_drop), int(seed),
+        _lib.stream_ptr())
+    _lib.check(rc, "dtds_attention_fwd")
+    return out, lse
+
+
+def attention_bwd(qkv, out, dout, lse, B, S, heads, *, scale, causal=False, key_bias=None,
+                  alibi=None, p_drop=0.0, seed=0):
+    """Returns dqkv [B*S, 3H]."""
+    H = qkv.shape[1] // 3
+    d = H // heads
+    if not _lib.use_native(qkv):
+        qkv_f = qkv.detach().float().requires_grad_(True)
+        q, k, v = _split_qkv(qkv_f, B, S, heads)
+        o, _ = ref.attention(q, k, v, scale=scale, causal=causal, key_bias=key_bias,
+                             alibi_slopes=alibi, p_drop=p_drop, seed=seed)
+        o = o.transpose(1, 2).reshape(B * S, H)
+        (g,) = torch.autograd.grad(o, qkv_f, dout.float())
+        return g.to(qkv.dtype)
+    dout = _c(dout)
+    dqkv = torch.empty(B * S, 3 * H, dtype=qkv.dtype, device=qkv.device)
+    delta = torch.empty(B, heads, S, dtype=torch.float32, device=qkv.device)
+    rc = _lib.lib().dtds_attention_bwd(
+        qkv.data_ptr(), qkv.stride(0), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
+        delta.data_ptr(), dqkv.data_ptr(), _lib.ptr(key_bias), _lib.ptr(alibi), B, S, heads, d,
+        float(scale), int(causal), float(p_drop), int(seed), _lib.stream_ptr())
+    _lib.check(rc, "dtds_attention_bwd")
+    return dqkv

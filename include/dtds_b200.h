@@ -1,0 +1,106 @@
+/* C ABI of libdtds_b200.so — the hand-written sm_100a kernels and the symmetric-memory runtime.
+ *
+ * Every function returns 0 on success and a non-zero code (a cudaError_t value, or a small
+ * negative number for argument errors, with a message on stderr) otherwise.  All device pointers
+ * are plain `void*`; bf16 tensors are row-major unless noted; `stream` is a cudaStream_t.
+ * Python reaches these through ctypes (distributed-training-and-deepspeed_b200/ops/_lib.py).
+ *
+ * Each block cites what it replaces in the reference (paths relative to /root/reference).
+ */
+#ifndef DTDS_B200_H_
+#define DTDS_B200_H_
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Activation codes shared by the GEMM epilogue and the standalone kernels. */
+#define DTDS_ACT_NONE 0
+#define DTDS_ACT_RELU 1      /* model/transformer.py:52 (OPT) */
+#define DTDS_ACT_GELU_ERF 2  /* HF BERT hidden_act="gelu" (model/bert_mp.py:22-24) */
+#define DTDS_ACT_GELU_TANH 3 /* BLOOM (zero_dp_training.py:117) */
+
+/* ---- tcgen05 / TMEM / TMA GEMM (replaces cuBLAS behind nn.Linear: model/transformer.py:37-40,
+ *      50-51; BertLayer / BertOnlyMLMHead in model/bert_mp.py:22-24) -------------------------
+ * D[M,N] = act(alpha * A·Bᵀ + bias) (+ residual), A logical [M,K], B logical [N,K].
+ * x_mn_major = 0: the operand is stored with K contiguous; 1: stored as [K, M|N] (M|N contiguous).
+ * Leading dimensions are in elements and must be multiples of 8; pointers 16-byte aligned.   */
+int dtds_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N, int K,
+                   int lda, int ldb, int ldd, int a_mn_major, int b_mn_major, int act,
+                   int out_fp32, cudaStream_t stream);
+/* Full form.  pre_out: also store the pre-activation (bf16, same ld as D).  dact_in: multiply the
+ * result by act'(dact_in) (backward through an activation).  accumulate: D += result.
+ * block_n: 0 = auto, or 64/128/256.  max_ctas: 0 = all SMs (lower it to leave SMs to a
+ * concurrent communication kernel).  ready_flags/ready_epoch/rows_per_flag: all-gather fused
+ * mode — rows [f*rows_per_flag, (f+1)*rows_per_flag) of B may only be read once
+ * ready_flags[f] >= ready_epoch (see dtds_allgather_rows_async).                              */
+int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const void* bias,
+                      const void* residual, void* pre_out, const void* dact_in, int M, int N,
+                      int K, int lda, int ldb, int ldd, int ld_res, int ld_dact, int a_mn_major,
+                      int b_mn_major, int act, int out_fp32, int accumulate, float alpha,
+                      int block_n, int max_ctas, const void* ready_flags, unsigned ready_epoch,
+                      int rows_per_flag, cudaStream_t stream);
+
+/* ---- LayerNorm (+dropout +residual), activations, dropout, softmax, column sums, MSE
+ *      (ATen kernels behind model/transformer.py:36,43-53; BERT post-LN blocks) ------------- */
+int dtds_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta,
+                       void* y, void* z_out, float* mean, float* rstd, int rows, int cols,
+                       float eps, float p_drop, unsigned long long seed, cudaStream_t stream);
+int dtds_layernorm_bwd_blocks(int rows, int cols); /* rows of `partial` the backward needs */
+int dtds_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd,
+                       const void* gamma, const void* dz_extra, void* dz, void* dx_drop,
+                       void* dgamma, void* dbeta, float* partial, int rows, int cols, float p_drop,
+                       unsigned long long seed, int grads_fp32, int accumulate,
+                       cudaStream_t stream);
+int dtds_colsum(const void* x, int rows, int cols, int ld, float* scratch, void* out, int out_fp32,
+                int accumulate, cudaStream_t stream);
+int dtds_act_fwd(const void* x, void* y, size_t n, int act, cudaStream_t stream);
+int dtds_act_bwd(const void* dy, const void* x, void* dx, size_t n, int act, cudaStream_t stream);
+int dtds_dropout(const void* x, const void* residual, void* y, size_t n, float p,
+                 unsigned long long seed, cudaStream_t stream);
+int dtds_softmax_rows(const void* x, const void* dy, void* out, int rows, int cols,
+                      cudaStream_t stream);
+int dtds_mse(const void* x, const void* t, void* dx, float* loss, size_t n, float gscale,
+             cudaStream_t stream); /* estimate_transformer_memory.py:114-120 */
+
+/* ---- Embedding, cross-entropy, Adam (BertEmbeddings model/bert_mp.py:22; CrossEntropyLoss
+ *      model_parallel_training.py:51,73; FusedAdam zero_dp_training.py:28-33; AdamW
+ *      data_parallel_training.py:34, model_parallel_training.py:50) ------------------------- */
+int dtds_embedding_fwd(const long long* ids, const long long* type_ids, const void* word,
+                       const void* pos, const void* type, void* out, int tokens, int seq,
+                       int hidden, int pos_offset, int vocab, cudaStream_t stream);
+int dtds_embedding_bwd(const long long* ids, const void* dout, void* dword, void* dpos, int batch,
+                       int seq, int hidden, int pos_offset, int vocab, int grads_fp32,
+                       int accumulate_pos, cudaStream_t stream);
+int dtds_cross_entropy(const void* logits, const long long* labels, void* dlogits, float* stats,
+                       float* row_loss, int rows, int vocab, int ld, int seq, int shift,
+                       long long ignore_index, float gscale, cudaStream_t stream);
+int dtds_adam_flat(float* p, void* p_lp, const void* g, float* m, float* v, size_t n, int* step,
+                   int inc_step, int grad_fp32, float lr, float beta1, float beta2, float eps,
+                   float weight_decay, float grad_scale, int adamw_mode, int bias_correction,
+                   cudaStream_t stream);
+int dtds_cast(const void* src, void* dst, size_t n, int to_bf16, cudaStream_t stream);
+
+/* ---- Fused attention on tcgen05 (replaces bmm -> Softmax -> Dropout -> bmm,
+ *      model/transformer.py:80-86, and HF BertSelfAttention / BLOOM / OPT attention) ----------
+ * qkv: [B*S, ld_qkv] bf16 rows = tokens, columns = [Q(H) | K(H) | V(H)], H = heads*64.
+ * out: [B*S, H].  lse: [B, heads, S] fp32.  key_bias: [B,S] additive fp32 or NULL (padding mask).
+ * alibi_slopes: [heads] fp32 or NULL.  Requires head_dim == 64 and S % 128 == 0.
+ * Backward writes dqkv [B*S, 3H]; `delta` is [B, heads, S] fp32 scratch supplied by the caller. */
+int dtds_attention_fwd(const void* qkv, int ld_qkv, void* out, float* lse, const float* key_bias,
+                       const float* alibi_slopes, int B, int S, int heads, int head_dim,
+                       float scale, int causal, float p_drop, unsigned long long seed,
+                       cudaStream_t stream);
+int dtds_attention_bwd(const void* qkv, int ld_qkv, const void* out, const void* dout,
+                       const float* lse, float* delta, void* dqkv, const float* key_bias,
+                       const float* alibi_slopes, int B, int S, int heads, int head_dim,
+                       float scale, int causal, float p_drop, unsigned long long seed,
+                       cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTDS_B200_H_ */
