@@ -1,0 +1,288 @@
+#!/usr/bin/env python
+"""Headline benchmark: BERT-base MLM data-parallel training throughput (samples/s).
+
+Config = the reference's data_parallel_training.py defaults (BASELINE.json config 3): HF-shaped
+BertForMaskedLM bert-base-cased, per-rank batch 4, sequence 512, AdamW lr 5e-5, DDP bucket 25 MiB,
+bf16 compute with fp32 master weights, synthetic MLM token batches, random-init weights.
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29511 bench.py --gpus 8 --steps 20 --warmup 5
+    python bench.py --impl reference ...      # the unmodified reference (unavailable offline)
+    python bench.py --impl torch ...          # stand-in baseline: HF BERT + torch DDP + AdamW
+
+Prints ONE JSON line (rank 0).  `value` is device-timed (CUDA events, max over ranks) over exactly
+--steps replays of the captured training step; `e2e` re-measures the same steps through the
+public API including the per-step pinned-host -> device input copy and device -> host loss read.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"])
+    ap.add_argument("--model", default="base", choices=["base", "large", "tiny"])
+    ap.add_argument("--batch-size", type=int, default=4, help="per-rank batch (reference default 4)")
+    ap.add_argument("--seq-len", type=int, default=512)
+    ap.add_argument("--bucket-size", type=int, default=25)
+    ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--comm", default=None, choices=[None, "custom", "nccl"])
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.proc = gpu_index, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = [c for c in sm if c > 0.5 * max(mx or [1])] or sm
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def reference_arm(args):
+    """The unmodified reference lives (if it could be installed) under baseline/_ref.  It has no
+    setup.py/pyproject.toml, imports transformers.AdamW (removed) and downloads bert-base-cased and
+    wikitext from the hub at start-up, so it cannot run in this offline image; see DESIGN.md."""
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    why = None
+    if not os.path.isdir(ref_dir) or not os.listdir(ref_dir):
+        why = ("reference not installable: /root/reference has no setup.py/pyproject.toml "
+               "(pip: 'neither setup.py nor pyproject.toml found'); its script also needs the removed "
+               "transformers.AdamW and hub downloads (no network)")
+    else:
+        sys.path.insert(0, ref_dir)
+        try:
+            import data_parallel_training  # noqa: F401
+            why = "reference imported but requires hub downloads of bert-base-cased and wikitext (no network)"
+        except Exception as e:  # noqa: BLE001
+            why = f"reference import failed: {type(e).__name__}: {str(e)[:120]}"
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+def make_batches(n, B, S, vocab, seed):
+    """Synthetic MLM batches in pinned host memory: 15 % of positions carry a label, rest -100."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.randint(1000, vocab, (n, B, S), generator=g, dtype=torch.int64)
+    labels = torch.full((n, B, S), -100, dtype=torch.int64)
+    mask = torch.rand((n, B, S), generator=g) < 0.15
+    labels[mask] = ids[mask]
+    ids[mask] = 103  # [MASK]
+    return ids.pin_memory(), labels.pin_memory()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus or world == 1 and args.gpus == 1, f"WORLD_SIZE {world} != --gpus {args.gpus}"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if args.comm:
+        os.environ["DTDS_COMM"] = args.comm
+
+    import dtds_b200  # noqa: F401
+    from dtds_b200 import comm
+    from dtds_b200.models import build_model, get_config
+    from dtds_b200.ops import _lib
+
+    if world > 1:
+        comm.init_process_group(backend="nccl")
+    model_name = {"base": "bert-base-cased", "large": "bert-large-cased", "tiny": "bert-tiny"}[args.model]
+    cfg = get_config(model_name)
+    B, S = args.batch_size, min(args.seq_len, cfg.max_position_embeddings)
+    n_batches = args.steps + args.warmup
+    ids_h, labels_h = make_batches(n_batches, B, S, cfg.vocab_size, seed=1234 + rank)
+    torch.manual_seed(0)
+
+    if args.impl == "torch":
+        step_eager, step_graph, launches_per_step, describe = build_torch_baseline(args, cfg, dev, world, local)
+    else:
+        step_eager, step_graph, launches_per_step, describe = build_ours(args, cfg, dev, world, ids_h, labels_h)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- device-timed region: exactly K steps -----------------------------------
+    ids_d, labels_d = ids_h.to(dev), labels_h.to(dev)
+    for i in range(args.warmup):
+        step_graph(ids_d[i], labels_d[i])
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        loss = step_graph(ids_d[args.warmup + i], labels_d[args.warmup + i])
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    final_loss = float(loss.item())
+
+    # ---------------- end-to-end region through the public API -------------------------------
+    loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
+    barrier()
+    t0 = time.perf_counter()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for i in range(args.steps):
+        loss = step_graph(ids_h[args.warmup + i], labels_h[args.warmup + i])   # H2D from pinned memory
+        loss_host.copy_(loss.float(), non_blocking=True)                       # D2H of the step result
+        torch.cuda.current_stream().synchronize()
+    f1.record()
+    barrier()
+    e2e_wall_ms = (time.perf_counter() - t0) * 1e3
+    e2e_ms = max(f0.elapsed_time(f1), e2e_wall_ms)
+
+    t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = t.tolist()
+    global_batch = B * world
+    value = global_batch * args.steps / (ms / 1e3)
+    e2e_value = global_batch * args.steps / (e2e_ms / 1e3)
+    out = {
+        "metric": "train samples/sec (DDP BERT MLM, data_parallel_training.py)",
+        "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic MLM token batches (15% masked), random-init weights",
+        "impl": args.impl,
+        "config": {"model": cfg.name, "global_batch": global_batch, "per_gpu_batch": B, "seq_len": S,
+                   "parallelism": f"dp{world}", "bucket_cap_mb": args.bucket_size, "optimizer": "AdamW lr=5e-5",
+                   "l2": "per-step working set (params+grads+Adam state+activations, >2 GB) exceeds the 126 MB L2; "
+                         "no explicit flush", **describe},
+        "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": e2e_ms / args.steps,
+                "h2d_bytes_per_step": 2 * B * S * 8, "d2h_bytes_per_step": 4},
+        "gpu_launches": launches_per_step * args.steps,
+        "final_loss": final_loss,
+    }
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def build_ours(args, cfg, dev, world, ids_h, labels_h):
+    import torch
+    from dtds_b200.models import build_model
+    from dtds_b200.ops import _lib
+    from dtds_b200.optim import HFAdamW
+    from dtds_b200.parallel.ddp import DistributedDataParallel
+    from dtds_b200.parallel.graph import GraphedStep
+
+    model = build_model(cfg).to(device=dev, dtype=torch.bfloat16)
+    model.train()
+    net = DistributedDataParallel(model, device_ids=[dev.index], bucket_cap_mb=args.bucket_size) if world > 1 else model
+    opt = HFAdamW(model.parameters(), lr=5e-5)
+
+    def train_step(ids, labels):
+        opt.zero_grad()
+        loss = net(ids, labels=labels).loss
+        loss.backward()
+        opt.step()
+        return loss
+
+    ex = [ids_h[0].to(dev), labels_h[0].to(dev)]
+    n0 = _lib.launch_count()
+    train_step(*ex)
+    per_step = _lib.launch_count() - n0
+    if args.no_graph:
+        return train_step, train_step, per_step, {"execution": "eager launches", "native_kernels": True}
+    gs = GraphedStep(train_step, ex, warmup=2)
+    return train_step, gs, per_step, {"execution": "whole step replayed as one CUDA graph", "native_kernels": True}
+
+
+def build_torch_baseline(args, cfg, dev, world, local):
+    """Stand-in for the reference's stack on this image: HF BertForMaskedLM (random init from the
+    in-repo config) + torch DistributedDataParallel over NCCL + torch.optim.AdamW, bf16 autocast."""
+    import torch
+    from transformers import BertConfig, BertForMaskedLM
+    hf_cfg = BertConfig(vocab_size=cfg.vocab_size, hidden_size=cfg.hidden_size, num_hidden_layers=cfg.num_hidden_layers,
+                        num_attention_heads=cfg.num_attention_heads, intermediate_size=cfg.intermediate_size,
+                        max_position_embeddings=cfg.max_position_embeddings)
+    model = BertForMaskedLM(hf_cfg).to(dev)
+    model.train()
+    net = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], bucket_cap_mb=args.bucket_size) if world > 1 else model
+    opt = torch.optim.AdamW(model.parameters(), lr=5e-5, eps=1e-6, weight_decay=0.0)
+
+    def train_step(ids, labels):
+        ids, labels = ids.to(dev, non_blocking=True), labels.to(dev, non_blocking=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = net(input_ids=ids, labels=labels).loss
+        loss.backward()
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        return loss
+
+    return train_step, train_step, 0, {"execution": "torch eager (HF BERT + torch DDP/NCCL + AdamW, bf16 autocast)",
+                                       "native_kernels": False}
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -90,17 +90,22 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         res = subprocess.run(cmd, capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError(f"link failed:\n{res.stdout}\n{res.stderr}")
+    (LIB_DIR / "build.sha").write_text(_combined_digest())
     return LIB_PATH
 
 
-def is_stale() -> bool:
-    if not LIB_PATH.exists():
-        return True
+def _combined_digest() -> str:
+    h = hashlib.sha256()
     for src in sources():
-        stamp = OBJ_DIR / (src.stem + ".sha")
-        if not stamp.exists() or stamp.read_text() != _digest(src):
-            return True
-    return False
+        h.update(_digest(src).encode())
+    return h.hexdigest()
+
+
+def is_stale() -> bool:
+    """True if the .so is missing or was built from different sources (lib/build.sha travels
+    with the .so to the GPU box; the object files do not)."""
+    stamp = LIB_DIR / "build.sha"
+    return not (LIB_PATH.exists() and stamp.exists() and stamp.read_text() == _combined_digest())
 
 
 if __name__ == "__main__":

@@ -8,8 +8,9 @@
 // output [B·S, 3H] through one TMA tensor map (no head-major transposes), and the context is
 // written token-major [B·S, H] ready for the output projection GEMM.
 //
-// Three kernels, all 6 warps: warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM owner),
-// warps 2..5 = 128 softmax threads, one per TMEM lane (= one score-matrix row each):
+// Three kernels, all 10 warps: warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM owner),
+// warps 2..9 = 256 softmax threads: two per TMEM lane (= score-matrix row), each owning 64 of the
+// 128 columns of a block (a warp may only touch the TMEM lane quadrant warp_id % 4):
 //   attn_fwd_kernel      CTA = (128 queries, head); loops over key blocks, online softmax.
 //   attn_bwd_dq_kernel   CTA = (128 queries, head); recomputes P, dS -> dQ.
 //   attn_bwd_dkdv_kernel CTA = (128 keys,    head); works on Sᵀ so that Pᵀ and dSᵀ come out of
@@ -27,7 +28,7 @@
 
 namespace dtds {
 
-constexpr int kAttnThreads = 192;
+constexpr int kAttnThreads = 320;
 constexpr int kTile = 128 * 64 * 2;  // one [128 x 64] bf16 tile = 16 KiB
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -40,18 +41,33 @@ struct AttnParams {
   const float* alibi;     // [heads] slopes or null
   float p_drop;
   unsigned long long seed;
+  const unsigned long long* seed_dev;  // optional device-side seed offset (CUDA graphs)
   __nv_bfloat16* out;  // fwd: [B*S, H]
   float* lse;          // [B, heads, S] natural-log logsumexp of the biased, scaled scores
   const float* delta;  // bwd: [B, heads, S] rowsum(dO * O)
   __nv_bfloat16* dqkv;  // bwd: [B*S, 3H]
 };
 
-__device__ __forceinline__ float attn_keep(const AttnParams& p, int bh, int iq, int jk,
-                                           float inv_keep) {
-  if (p.p_drop <= 0.f) return 1.f;
-  const uint64_t idx = (static_cast<uint64_t>(bh) * p.S + iq) * p.S + jk;
-  const float u = (hash_u32(p.seed, idx) >> 8) * (1.0f / 16777216.0f);
-  return u >= p.p_drop ? inv_keep : 0.f;
+// Dropout keep-scales for 32 consecutive keys [jk0, jk0+32) of query row iq (jk0 even).
+__device__ __forceinline__ void attn_keep32(const DropRng& rng, const AttnParams& p, int bh, int iq,
+                                            int jk0, float (&ks)[32]) {
+  const uint64_t pair0 = ((static_cast<uint64_t>(bh) * p.S + iq) * p.S + jk0) >> 1;
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const uint32_t b = drop_bits(rng, pair0 + k);
+    ks[2 * k] = (b & 0xFFFFu) >= rng.thr ? rng.inv_keep : 0.f;
+    ks[2 * k + 1] = (b >> 16) >= rng.thr ? rng.inv_keep : 0.f;
+  }
+}
+// Single element (used where consecutive elements are not consecutive keys: the transposed kernel).
+__device__ __forceinline__ float attn_keep1(const DropRng& rng, const AttnParams& p, int bh, int iq,
+                                            int jk) {
+  return drop_scale1(rng, (static_cast<uint64_t>(bh) * p.S + iq) * p.S + jk);
+}
+__device__ __forceinline__ DropRng attn_rng(const AttnParams& p) {
+  const uint64_t seed =
+      p.seed + (p.seed_dev != nullptr ? *p.seed_dev * 0xD1B54A32D192ED03ull : 0ull);
+  return make_drop_rng(seed, p.p_drop);
 }
 
 // Writes 32 consecutive columns [col0, col0+32) of row `row` of a [128 x 128] bf16 operand tile
@@ -102,6 +118,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
   uint64_t* p_full = bars + 6;
   uint64_t* o_full = bars + 7;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  __nv_bfloat16* sMax = reinterpret_cast<__nv_bfloat16*>(bars + 9);  // [2 halves][128 rows]
   check_smem_alignment(smem);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -115,7 +132,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     mbar_init(q_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
     mbar_init(s_full, 1);
-    mbar_init(p_full, 4);
+    mbar_init(p_full, 8);
     mbar_init(o_full, 1);
     fence_mbar_init();
   }
@@ -162,15 +179,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       }
     }
   } else {
-    const int q = warp & 3;
+    const int q = warp & 3;              // TMEM lane quadrant
+    const int half = (warp - 2) >> 2;    // which 64 of the 128 key columns of a block
     const int r = q * 32 + lane;
     const int iq = qb * 128 + r;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     const float scale_l2 = p.scale * kLog2e;
     const float slope_l2 = p.alibi != nullptr ? p.alibi[h] * kLog2e : 0.f;
-    const float inv_keep = p.p_drop > 0.f ? 1.f / (1.f - p.p_drop) : 1.f;
+    const DropRng rng = attn_rng(p);
     const float* kb = p.key_bias != nullptr ? p.key_bias + static_cast<size_t>(b) * p.S : nullptr;
-    float m = -INFINITY, l = 0.f;
+    float m = -INFINITY, l = 0.f;  // l: partial row sum over this thread's columns
     uint32_t regs[32];
     float v[32];
     for (int j = 0; j < nkv; ++j) {
@@ -185,13 +203,21 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       };
       float mx = -INFINITY;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        tmem_ld_32x32(tS + lane_off + c * 32, regs);
+      for (int c = 0; c < 2; ++c) {
+        const int col = half * 64 + c * 32;
+        tmem_ld_32x32(tS + lane_off + col, regs);
         tmem_ld_wait();
 #pragma unroll
-        for (int t = 0; t < 32; ++t) mx = fmaxf(mx, score(regs[t], j * 128 + c * 32 + t));
+        for (int t = 0; t < 32; ++t) mx = fmaxf(mx, score(regs[t], j * 128 + col + t));
       }
-      const float m_new = fmaxf(m, mx);
+      // Row max across the two column halves.  Exchanged rounded to bf16: softmax only needs both
+      // halves to subtract the SAME value close to the true max, and 2 bytes keep the CTA within
+      // the shared-memory budget of two CTAs per SM.
+      named_bar_sync(2, 256);  // previous block's readers are done with sMax
+      sMax[half * 128 + r] = __float2bfloat16_ru(mx);
+      named_bar_sync(1, 256);
+      const float mx_blk = fmaxf(__bfloat162float(sMax[r]), __bfloat162float(sMax[128 + r]));
+      const float m_new = fmaxf(m, mx_blk);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
       const float corr = exp2f(m - m_use);
       if (j > 0) {  // previous P·V must have finished reading sP and updating O
@@ -200,29 +226,32 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       }
       float rs = 0.f;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        tmem_ld_32x32(tS + lane_off + c * 32, regs);
+      for (int c = 0; c < 2; ++c) {
+        const int col = half * 64 + c * 32;
+        tmem_ld_32x32(tS + lane_off + col, regs);
         tmem_ld_wait();
 #pragma unroll
         for (int t = 0; t < 32; ++t) {
-          const int jk = j * 128 + c * 32 + t;
-          const float pr = exp2f(score(regs[t], jk) - m_use);
+          const float pr = exp2f(score(regs[t], j * 128 + col + t) - m_use);
           rs += pr;
-          v[t] = pr * attn_keep(p, bh, iq, jk, inv_keep);
+          v[t] = pr;
         }
-        store_chunk_sw128(sP, r, c * 32, v);
+        if (rng.thr != 0u) {
+          float ks[32];
+          attn_keep32(rng, p, bh, iq, j * 128 + col, ks);
+#pragma unroll
+          for (int t = 0; t < 32; ++t) v[t] *= ks[t];
+        }
+        store_chunk_sw128(sP, r, col, v);
       }
       l = l * corr + rs;
       m = m_new;
-      if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
-#pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
-          tmem_ld_32x32(tO + lane_off + c * 32, regs);
-          tmem_ld_wait();
+      if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {  // this half rescales 32 of O's 64 columns
+        tmem_ld_32x32(tO + lane_off + half * 32, regs);
+        tmem_ld_wait();
 #pragma unroll
-          for (int t = 0; t < 32; ++t) regs[t] = __float_as_uint(__uint_as_float(regs[t]) * corr);
-          tmem_st_32x32(tO + lane_off + c * 32, regs);
-        }
+        for (int t = 0; t < 32; ++t) regs[t] = __float_as_uint(__uint_as_float(regs[t]) * corr);
+        tmem_st_32x32(tO + lane_off + half * 32, regs);
         tmem_st_wait();
       }
       fence_async_shared();
@@ -232,24 +261,26 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     }
     mbar_wait(o_full, (nkv - 1) & 1);
     tc_fence_after();
-    const float inv_l = l > 0.f ? 1.f / l : 0.f;
-    __nv_bfloat16* dst = p.out + static_cast<size_t>(row0 + iq) * p.H + h * 64;
-#pragma unroll 1
-    for (int c = 0; c < 2; ++c) {
-      tmem_ld_32x32(tO + lane_off + c * 32, regs);
-      tmem_ld_wait();
+    // total row sum = sum of the two halves' partial sums (sP is free now: reuse it as scratch)
+    float* sL = reinterpret_cast<float*>(sP);
+    sL[half * 128 + r] = l;
+    named_bar_sync(1, 256);
+    const float l_tot = sL[r] + sL[128 + r];
+    const float inv_l = l_tot > 0.f ? 1.f / l_tot : 0.f;
+    __nv_bfloat16* dst = p.out + static_cast<size_t>(row0 + iq) * p.H + h * 64 + half * 32;
+    tmem_ld_32x32(tO + lane_off + half * 32, regs);
+    tmem_ld_wait();
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        float o[8];
+    for (int g = 0; g < 4; ++g) {
+      float o[8];
 #pragma unroll
-        for (int t = 0; t < 8; ++t) o[t] = __uint_as_float(regs[g * 8 + t]) * inv_l;
-        *reinterpret_cast<uint4*>(dst + c * 32 + g * 8) =
-            make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
-                       pack_bf16x2(o[6], o[7]));
-      }
+      for (int t = 0; t < 8; ++t) o[t] = __uint_as_float(regs[g * 8 + t]) * inv_l;
+      *reinterpret_cast<uint4*>(dst + g * 8) =
+          make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
+                     pack_bf16x2(o[6], o[7]));
     }
-    if (p.lse != nullptr)
-      p.lse[static_cast<size_t>(bh) * p.S + iq] = (l > 0.f) ? (m * kLn2 + __logf(l)) : -INFINITY;
+    if (p.lse != nullptr && half == 0)
+      p.lse[static_cast<size_t>(bh) * p.S + iq] = (l_tot > 0.f) ? (m * kLn2 + __logf(l_tot)) : -INFINITY;
   }
   tc_fence_before();
   __syncthreads();
@@ -308,7 +339,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     mbar_init(q_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
     mbar_init(s_full, 1);
-    mbar_init(ds_full, 4);
+    mbar_init(ds_full, 8);
     mbar_init(dq_done, 1);
     fence_mbar_init();
   }
@@ -359,12 +390,13 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     }
   } else {
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int r = q * 32 + lane;
     const int iq = qb * 128 + r;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     const float scale_l2 = p.scale * kLog2e;
     const float slope_l2 = p.alibi != nullptr ? p.alibi[h] * kLog2e : 0.f;
-    const float inv_keep = p.p_drop > 0.f ? 1.f / (1.f - p.p_drop) : 1.f;
+    const DropRng rng = attn_rng(p);
     const float* kb = p.key_bias != nullptr ? p.key_bias + static_cast<size_t>(b) * p.S : nullptr;
     const float lse = p.lse[static_cast<size_t>(bh) * p.S + iq];
     const float lse_l2 = lse * kLog2e;
@@ -379,22 +411,26 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
         tc_fence_after();
       }
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        tmem_ld_32x32(tS + lane_off + c * 32, rs);
-        tmem_ld_32x32(tdP + lane_off + c * 32, rp);
+      for (int c = 0; c < 2; ++c) {
+        const int col = half * 64 + c * 32;
+        tmem_ld_32x32(tS + lane_off + col, rs);
+        tmem_ld_32x32(tdP + lane_off + col, rp);
         tmem_ld_wait();
+        float ks[32];
+        if (rng.thr != 0u) attn_keep32(rng, p, bh, iq, j * 128 + col, ks);
 #pragma unroll
         for (int t = 0; t < 32; ++t) {
-          const int jk = j * 128 + c * 32 + t;
+          const int jk = j * 128 + col + t;
           float x = __uint_as_float(rs[t]) * scale_l2;
           if (p.alibi != nullptr) x += slope_l2 * static_cast<float>(jk - iq);
           if (kb != nullptr) x += kb[jk] * kLog2e;
           float pr = exp2f(x - lse_l2);
           if ((p.causal && jk > iq) || lse == -INFINITY) pr = 0.f;
-          const float dp = __uint_as_float(rp[t]) * attn_keep(p, bh, iq, jk, inv_keep);
+          float dp = __uint_as_float(rp[t]);
+          if (rng.thr != 0u) dp *= ks[t];
           v[t] = pr * (dp - dlt) * p.scale;
         }
-        store_chunk_sw128(sdS, r, c * 32, v);
+        store_chunk_sw128(sdS, r, col, v);
       }
       fence_async_shared();
       tc_fence_before();
@@ -403,19 +439,16 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     }
     mbar_wait(dq_done, (nkv - 1) & 1);
     tc_fence_after();
-    __nv_bfloat16* dst = p.dqkv + static_cast<size_t>(row0 + iq) * (3 * p.H) + h * 64;
-#pragma unroll 1
-    for (int c = 0; c < 2; ++c) {
-      tmem_ld_32x32(tdQ + lane_off + c * 32, rs);
-      tmem_ld_wait();
+    __nv_bfloat16* dst = p.dqkv + static_cast<size_t>(row0 + iq) * (3 * p.H) + h * 64 + half * 32;
+    tmem_ld_32x32(tdQ + lane_off + half * 32, rs);
+    tmem_ld_wait();
 #pragma unroll
-      for (int g = 0; g < 4; ++g)
-        *reinterpret_cast<uint4*>(dst + c * 32 + g * 8) = make_uint4(
-            pack_bf16x2(__uint_as_float(rs[g * 8 + 0]), __uint_as_float(rs[g * 8 + 1])),
-            pack_bf16x2(__uint_as_float(rs[g * 8 + 2]), __uint_as_float(rs[g * 8 + 3])),
-            pack_bf16x2(__uint_as_float(rs[g * 8 + 4]), __uint_as_float(rs[g * 8 + 5])),
-            pack_bf16x2(__uint_as_float(rs[g * 8 + 6]), __uint_as_float(rs[g * 8 + 7])));
-    }
+    for (int g = 0; g < 4; ++g)
+      *reinterpret_cast<uint4*>(dst + g * 8) = make_uint4(
+          pack_bf16x2(__uint_as_float(rs[g * 8 + 0]), __uint_as_float(rs[g * 8 + 1])),
+          pack_bf16x2(__uint_as_float(rs[g * 8 + 2]), __uint_as_float(rs[g * 8 + 3])),
+          pack_bf16x2(__uint_as_float(rs[g * 8 + 4]), __uint_as_float(rs[g * 8 + 5])),
+          pack_bf16x2(__uint_as_float(rs[g * 8 + 6]), __uint_as_float(rs[g * 8 + 7])));
   }
   tc_fence_before();
   __syncthreads();
@@ -459,7 +492,7 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
     mbar_init(kv_full, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&q_full[s], 1); mbar_init(&q_empty[s], 1); }
     mbar_init(st_full, 1);
-    mbar_init(pt_full, 4);
+    mbar_init(pt_full, 8);
     mbar_init(acc_done, 1);
     fence_mbar_init();
   }
@@ -513,12 +546,13 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
     }
   } else {
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;  // which 64 of the 128 query columns of a block
     const int r = q * 32 + lane;       // key row within the block
     const int jk = kb_idx * 128 + r;   // absolute key index
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     const float scale_l2 = p.scale * kLog2e;
     const float slope_l2 = p.alibi != nullptr ? p.alibi[h] * kLog2e : 0.f;
-    const float inv_keep = p.p_drop > 0.f ? 1.f / (1.f - p.p_drop) : 1.f;
+    const DropRng rng = attn_rng(p);
     const float kbias_l2 =
         p.key_bias != nullptr ? p.key_bias[static_cast<size_t>(b) * p.S + jk] * kLog2e : 0.f;
     uint32_t rs[32], rp[32];
@@ -527,9 +561,11 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
       const int i = i0 + it;
       // per-query statistics of this query block -> smem (previous readers are done: they
       // passed the named barrier at the end of the last iteration)
-      sLse[r] = p.lse[static_cast<size_t>(bh) * p.S + i * 128 + r] * kLog2e;
-      sDelta[r] = p.delta[static_cast<size_t>(bh) * p.S + i * 128 + r];
-      named_bar_sync(1, 128);
+      if (half == 0) {
+        sLse[r] = p.lse[static_cast<size_t>(bh) * p.S + i * 128 + r] * kLog2e;
+        sDelta[r] = p.delta[static_cast<size_t>(bh) * p.S + i * 128 + r];
+      }
+      named_bar_sync(1, 256);
       mbar_wait(st_full, it & 1);
       tc_fence_after();
       if (it > 0) {  // sPT / sdST are still being read by the previous accumulation MMAs
@@ -537,53 +573,51 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
         tc_fence_after();
       }
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        tmem_ld_32x32(tST + lane_off + c * 32, rs);
-        tmem_ld_32x32(tdPT + lane_off + c * 32, rp);
+      for (int c = 0; c < 2; ++c) {
+        const int col = half * 64 + c * 32;
+        tmem_ld_32x32(tST + lane_off + col, rs);
+        tmem_ld_32x32(tdPT + lane_off + col, rp);
         tmem_ld_wait();
 #pragma unroll
         for (int t = 0; t < 32; ++t) {
-          const int iq = i * 128 + c * 32 + t;
+          const int iq = i * 128 + col + t;
           float x = __uint_as_float(rs[t]) * scale_l2 + kbias_l2;
           if (p.alibi != nullptr) x += slope_l2 * static_cast<float>(jk - iq);
-          const float l2 = sLse[c * 32 + t];
+          const float l2 = sLse[col + t];
           float pr = exp2f(x - l2);
           if ((p.causal && jk > iq) || l2 == -INFINITY) pr = 0.f;
-          const float keep = attn_keep(p, bh, iq, jk, inv_keep);
+          const float keep = rng.thr != 0u ? attn_keep1(rng, p, bh, iq, jk) : 1.f;
           vp[t] = pr * keep;
-          vd[t] = pr * (__uint_as_float(rp[t]) * keep - sDelta[c * 32 + t]) * p.scale;
+          vd[t] = pr * (__uint_as_float(rp[t]) * keep - sDelta[col + t]) * p.scale;
         }
-        store_chunk_sw128(sPT, r, c * 32, vp);
-        store_chunk_sw128(sdST, r, c * 32, vd);
+        store_chunk_sw128(sPT, r, col, vp);
+        store_chunk_sw128(sdST, r, col, vd);
       }
       fence_async_shared();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(pt_full);
-      named_bar_sync(1, 128);  // everyone is done with sLse/sDelta before the next overwrite
+      named_bar_sync(2, 256);  // everyone is done with sLse/sDelta before the next overwrite
     }
     mbar_wait(acc_done, (niter - 1) & 1);
     tc_fence_after();
-    __nv_bfloat16* dk = p.dqkv + static_cast<size_t>(row0 + jk) * (3 * p.H) + p.H + h * 64;
+    __nv_bfloat16* dk = p.dqkv + static_cast<size_t>(row0 + jk) * (3 * p.H) + p.H + h * 64 + half * 32;
     __nv_bfloat16* dv = dk + p.H;
-#pragma unroll 1
-    for (int c = 0; c < 2; ++c) {
-      tmem_ld_32x32(tdK + lane_off + c * 32, rs);
-      tmem_ld_32x32(tdV + lane_off + c * 32, rp);
-      tmem_ld_wait();
+    tmem_ld_32x32(tdK + lane_off + half * 32, rs);
+    tmem_ld_32x32(tdV + lane_off + half * 32, rp);
+    tmem_ld_wait();
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        *reinterpret_cast<uint4*>(dk + c * 32 + g * 8) = make_uint4(
-            pack_bf16x2(__uint_as_float(rs[g * 8 + 0]), __uint_as_float(rs[g * 8 + 1])),
-            pack_bf16x2(__uint_as_float(rs[g * 8 + 2]), __uint_as_float(rs[g * 8 + 3])),
-            pack_bf16x2(__uint_as_float(rs[g * 8 + 4]), __uint_as_float(rs[g * 8 + 5])),
-            pack_bf16x2(__uint_as_float(rs[g * 8 + 6]), __uint_as_float(rs[g * 8 + 7])));
-        *reinterpret_cast<uint4*>(dv + c * 32 + g * 8) = make_uint4(
-            pack_bf16x2(__uint_as_float(rp[g * 8 + 0]), __uint_as_float(rp[g * 8 + 1])),
-            pack_bf16x2(__uint_as_float(rp[g * 8 + 2]), __uint_as_float(rp[g * 8 + 3])),
-            pack_bf16x2(__uint_as_float(rp[g * 8 + 4]), __uint_as_float(rp[g * 8 + 5])),
-            pack_bf16x2(__uint_as_float(rp[g * 8 + 6]), __uint_as_float(rp[g * 8 + 7])));
-      }
+    for (int g = 0; g < 4; ++g) {
+      *reinterpret_cast<uint4*>(dk + g * 8) = make_uint4(
+          pack_bf16x2(__uint_as_float(rs[g * 8 + 0]), __uint_as_float(rs[g * 8 + 1])),
+          pack_bf16x2(__uint_as_float(rs[g * 8 + 2]), __uint_as_float(rs[g * 8 + 3])),
+          pack_bf16x2(__uint_as_float(rs[g * 8 + 4]), __uint_as_float(rs[g * 8 + 5])),
+          pack_bf16x2(__uint_as_float(rs[g * 8 + 6]), __uint_as_float(rs[g * 8 + 7])));
+      *reinterpret_cast<uint4*>(dv + g * 8) = make_uint4(
+          pack_bf16x2(__uint_as_float(rp[g * 8 + 0]), __uint_as_float(rp[g * 8 + 1])),
+          pack_bf16x2(__uint_as_float(rp[g * 8 + 2]), __uint_as_float(rp[g * 8 + 3])),
+          pack_bf16x2(__uint_as_float(rp[g * 8 + 4]), __uint_as_float(rp[g * 8 + 5])),
+          pack_bf16x2(__uint_as_float(rp[g * 8 + 6]), __uint_as_float(rp[g * 8 + 7])));
     }
   }
   tc_fence_before();
@@ -592,7 +626,7 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
-constexpr int kFwdSmem = 7 * kTile + 128;
+constexpr int kFwdSmem = 7 * kTile + 72 + 512;  // tiles + barriers + bf16 row-max exchange
 constexpr int kDqSmem = 8 * kTile + 128;
 constexpr int kDkdvSmem = 10 * kTile + 1024 + 128;
 
@@ -614,7 +648,8 @@ using namespace dtds;
 extern "C" int dtds_attention_fwd(const void* qkv, int ld_qkv, void* out, float* lse,
                                   const float* key_bias, const float* alibi_slopes, int B, int S,
                                   int heads, int head_dim, float scale, int causal, float p_drop,
-                                  unsigned long long seed, cudaStream_t stream) {
+                                  unsigned long long seed, const unsigned long long* seed_dev,
+                                  cudaStream_t stream) {
   if (check_attn_args(B, S, heads, head_dim, ld_qkv)) return -1;
   const int H = heads * 64;
   CUtensorMap tm;
@@ -622,7 +657,7 @@ extern "C" int dtds_attention_fwd(const void* qkv, int ld_qkv, void* out, float*
   if (rc) return rc;
   AttnParams p{};
   p.B = B; p.S = S; p.heads = heads; p.H = H; p.scale = scale; p.causal = causal;
-  p.key_bias = key_bias; p.alibi = alibi_slopes; p.p_drop = p_drop; p.seed = seed;
+  p.key_bias = key_bias; p.alibi = alibi_slopes; p.p_drop = p_drop; p.seed = seed; p.seed_dev = seed_dev;
   p.out = static_cast<__nv_bfloat16*>(out); p.lse = lse;
   static bool attr_set = false;
   if (!attr_set) {
@@ -639,7 +674,7 @@ extern "C" int dtds_attention_bwd(const void* qkv, int ld_qkv, const void* out, 
                                   const float* lse, float* delta, void* dqkv, const float* key_bias,
                                   const float* alibi_slopes, int B, int S, int heads, int head_dim,
                                   float scale, int causal, float p_drop, unsigned long long seed,
-                                  cudaStream_t stream) {
+                                  const unsigned long long* seed_dev, cudaStream_t stream) {
   if (check_attn_args(B, S, heads, head_dim, ld_qkv)) return -1;
   const int H = heads * 64;
   CUtensorMap tm, tmdo;
@@ -649,7 +684,7 @@ extern "C" int dtds_attention_bwd(const void* qkv, int ld_qkv, const void* out, 
   if (rc) return rc;
   AttnParams p{};
   p.B = B; p.S = S; p.heads = heads; p.H = H; p.scale = scale; p.causal = causal;
-  p.key_bias = key_bias; p.alibi = alibi_slopes; p.p_drop = p_drop; p.seed = seed;
+  p.key_bias = key_bias; p.alibi = alibi_slopes; p.p_drop = p_drop; p.seed = seed; p.seed_dev = seed_dev;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
   static bool attr_set = false;
   if (!attr_set) {

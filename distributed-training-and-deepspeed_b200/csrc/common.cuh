@@ -312,27 +312,93 @@ __device__ __forceinline__ float block_max(float v, float* scratch) {
 }
 
 // ----------------------------------------------------------------------------- activations
+// tanh(u) = 1 - 2 / (exp(2u) + 1): one exp and one reciprocal; exact limits at +-inf.
+__device__ __forceinline__ float fast_tanh(float u) {
+  const float e2 = __expf(2.f * u);
+  return 1.f - __fdividef(2.f, e2 + 1.f);
+}
+// erf via Abramowitz-Stegun 7.1.26 (|error| < 1.5e-7): one reciprocal, one exp, five FMAs.  The
+// library erff costs several times more and made GEMM epilogues with GELU epilogue-bound.
+// `e` returns exp(-x*x) so callers needing the Gaussian density can reuse it.
+__device__ __forceinline__ float fast_erf(float x, float& e) {
+  const float ax = fabsf(x);
+  const float t = __fdividef(1.f, fmaf(0.3275911f, ax, 1.f));
+  e = __expf(-ax * ax);
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float y = fmaf(-poly * t, e, 1.f);
+  return copysignf(y, x);
+}
 __device__ __forceinline__ float gelu_erf(float x) {
-  return 0.5f * x * (1.f + erff(x * 0.70710678118654752f));
+  float e;
+  return 0.5f * x * (1.f + fast_erf(x * 0.70710678118654752f, e));
 }
 __device__ __forceinline__ float gelu_erf_grad(float x) {
-  const float cdf = 0.5f * (1.f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.39894228040143268f * __expf(-0.5f * x * x);
-  return cdf + x * pdf;
+  float e;  // = exp(-x^2 / 2)
+  const float cdf = 0.5f * (1.f + fast_erf(x * 0.70710678118654752f, e));
+  return fmaf(x * 0.39894228040143268f, e, cdf);
 }
 __device__ __forceinline__ float gelu_tanh(float x) {
   const float u = 0.79788456080286536f * (x + 0.044715f * x * x * x);
-  return 0.5f * x * (1.f + tanhf(u));
+  return 0.5f * x * (1.f + fast_tanh(u));
 }
 __device__ __forceinline__ float gelu_tanh_grad(float x) {
   const float x2 = x * x;
   const float u = 0.79788456080286536f * (x + 0.044715f * x * x2);
-  const float t = tanhf(u);
+  const float t = fast_tanh(u);
   const float du = 0.79788456080286536f * (1.f + 3.f * 0.044715f * x2);
   return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
 }
 
-// Counter-based RNG for dropout: one 64-bit mix per (seed, offset) -> uniform in [0,1).
+// Counter-based RNG for dropout: 16 random bits per element, two elements per 32-bit hash.
+//   key  = lo32(seed) ^ mix32(hi32(seed) + hi32(pair) * 0x85EBCA77)      (pair = element_index / 2)
+//   bits = mix32(key ^ lo32(pair) * 0x9E3779B1);  even element -> low half, odd -> high half
+// keep <=> bits16 >= floor(p * 65536).  Masks are a pure function of (seed, element index): the
+// backward pass recomputes them, nothing is stored.  ops/reference.py implements the same.
+__device__ __forceinline__ uint32_t mix32(uint32_t h) {
+  h ^= h >> 16;
+  h *= 0x85EBCA6Bu;
+  h ^= h >> 13;
+  h *= 0xC2B2AE35u;
+  h ^= h >> 16;
+  return h;
+}
+struct DropRng {
+  uint32_t seed_lo, seed_hi, thr;
+  float inv_keep;
+};
+__device__ __forceinline__ DropRng make_drop_rng(uint64_t seed, float p) {
+  DropRng r;
+  r.seed_lo = static_cast<uint32_t>(seed);
+  r.seed_hi = static_cast<uint32_t>(seed >> 32);
+  r.thr = p > 0.f ? static_cast<uint32_t>(p * 65536.f) : 0u;
+  r.inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  return r;
+}
+// 32 random bits covering elements 2*pair and 2*pair+1.
+__device__ __forceinline__ uint32_t drop_bits(const DropRng& r, uint64_t pair) {
+  const uint32_t key = r.seed_lo ^ mix32(r.seed_hi + static_cast<uint32_t>(pair >> 32) * 0x85EBCA77u);
+  return mix32(key ^ (static_cast<uint32_t>(pair) * 0x9E3779B1u));
+}
+// Keep-scale of a single element (slow path: scalar tails).
+__device__ __forceinline__ float drop_scale1(const DropRng& r, uint64_t idx) {
+  if (r.thr == 0u) return 1.f;
+  const uint32_t b = drop_bits(r, idx >> 1);
+  const uint32_t u = (idx & 1) ? (b >> 16) : (b & 0xFFFFu);
+  return u >= r.thr ? r.inv_keep : 0.f;
+}
+// Keep-scales of 8 consecutive elements starting at an even index.
+__device__ __forceinline__ void drop_scale8(const DropRng& r, uint64_t idx0, float (&s)[8]) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t b = drop_bits(r, (idx0 >> 1) + k);
+    s[2 * k] = (b & 0xFFFFu) >= r.thr ? r.inv_keep : 0.f;
+    s[2 * k + 1] = (b >> 16) >= r.thr ? r.inv_keep : 0.f;
+  }
+}
+// Legacy 64-bit mixer (still used to derive per-call seeds on the host side of tests).
 __device__ __forceinline__ uint32_t hash_u32(uint64_t seed, uint64_t idx) {
   uint64_t z = seed + idx * 0x9E3779B97F4A7C15ull;
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;

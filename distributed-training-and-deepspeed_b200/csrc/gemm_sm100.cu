@@ -11,7 +11,8 @@
 // Structure: persistent kernel, one CTA per SM, 6 warps:
 //   warp 0      TMA producer    (cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx)
 //   warp 1      MMA issuer      (one thread issues tcgen05.mma, accumulators in TMEM, 2 stages)
-//   warps 2..5  epilogue        (tcgen05.ld -> bias / activation / residual -> global)
+//   warps 2..9  epilogue        (tcgen05.ld -> bias / activation / residual -> global); two warps
+//                               per TMEM lane quadrant, each taking half of the tile's columns
 // The epilogue of tile i overlaps the main loop of tile i+1 through the double-buffered TMEM
 // accumulator.  When `peer_flags` is given (ZeRO-3 all-gather fused GEMM) the producer waits on
 // the per-chunk arrival flag of the B rows it is about to load; see fused_comm.cu.
@@ -30,7 +31,7 @@ namespace dtds {
 
 constexpr int kBM = 128;
 constexpr int kBK = 64;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps
 
 template <int BN>
 struct GemmCfg {
@@ -93,7 +94,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 4);
+      mbar_init(&tmem_empty[s], 8);
     }
     fence_mbar_init();
   }
@@ -190,7 +191,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps
-    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    const int q = warp & 3;          // TMEM lane quadrant this warp may access
+    const int chalf = (warp - 2) >> 2;  // which half of the tile's column chunks this warp owns
+    constexpr int kChunksPerWarp = BN / 64;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int m0 = (tile % num_m) * kBM;
@@ -203,7 +206,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const bool row_ok = row < p.M;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int cc = 0; cc < kChunksPerWarp; ++cc) {
+        const int c = chalf * kChunksPerWarp + cc;
         const int col0 = n0 + c * 32;
         if (col0 >= p.N) break;  // warp-uniform
         uint32_t r[32];
@@ -349,6 +353,15 @@ static EncodeTiledFn get_encode_fn() {
 // Builds a 2-D bf16 tensor map with 128B swizzle.  dim0 is the contiguous dimension.
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1,
                       uint64_t ld_elems, uint32_t box0, uint32_t box1) {
+  // cuTensorMapEncodeTiled is a driver call: it needs a current context on THIS thread.  PyTorch's
+  // autograd worker threads may not have one yet (device 0 is "current" by default without its
+  // primary context being bound), so bind it through the runtime once per thread.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaSetDevice(dev);
+    ctx_bound = true;
+  }
   EncodeTiledFn fn = get_encode_fn();
   if (fn == nullptr) {
     fprintf(stderr, "[dtds] cuTensorMapEncodeTiled entry point not available\n");
@@ -407,19 +420,34 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   return 0;
 }
 
-static int pick_block_n(int M, int N, int requested) {
+// Picks BLOCK_N with a small cost model.  At the token counts of the reference's scripts
+// (2048 rows per rank) most GEMMs have fewer than two waves of tiles and are bound by the
+// L2 -> shared-memory fill rate rather than by the tensor pipe, so "enough tiles for every SM" is
+// the wrong criterion: a 128-wide tile moves 2/3 of the bytes of two 64-wide ones.
+static int pick_block_n(int M, int N, int K, int requested) {
   if (requested == 64 || requested == 128 || requested == 256) return requested;
   const int sms = sm_count();
   const int num_m = (M + kBM - 1) / kBM;
-  // Largest tile that still gives every SM at least one tile; otherwise the smallest tile.
+  const int num_kb = (K + kBK - 1) / kBK;
   const int cands[3] = {256, 128, 64};
+  double best = 1e30;
+  int best_bn = 64;
   for (int i = 0; i < 3; ++i) {
     const int bn = cands[i];
-    if (bn > 64 && N < bn) continue;
+    if (bn > 64 && N <= bn / 2) continue;
     const int tiles = num_m * ((N + bn - 1) / bn);
-    if (tiles >= sms) return bn;
+    const int rounds = (tiles + sms - 1) / sms;
+    const int active = tiles < sms ? tiles : sms;
+    double bw = 6300.0 / active;          // chip-wide L2 fill rate shared by the active SMs
+    if (bw > 72.0) bw = 72.0;             // per-SM ceiling (bytes / clock)
+    const double fill = (16384.0 + bn * 128.0) / bw;
+    const double mma = 2.0 * bn;          // 4 MMAs of K=16 per k-block, bn/2 clocks each
+    const double per_kb = fill > mma ? fill : mma;
+    const double epi = 40.0 * bn / 8 + 600;  // drain of one tile, overlapped except for the last
+    const double t = rounds * (num_kb * per_kb) + epi + 1500;
+    if (t < best) { best = t; best_bn = bn; }
   }
-  return 64;
+  return best_bn;
 }
 
 }  // namespace dtds
@@ -443,7 +471,7 @@ extern "C" int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const vo
             lda, ldb, ldd);
     return -3;
   }
-  const int bn = pick_block_n(M, N, block_n);
+  const int bn = pick_block_n(M, N, K, block_n);
   CUtensorMap tmA, tmB;
   int rc;
   if (!a_mn_major) rc = make_tmap_2d_bf16(&tmA, A, K, M, lda, kBK, kBM);

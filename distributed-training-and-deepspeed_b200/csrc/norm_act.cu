@@ -11,13 +11,6 @@
 
 namespace dtds {
 
-__device__ __forceinline__ float dropout_keep_scale(uint64_t seed, uint64_t idx, float p,
-                                                    float inv_keep) {
-  if (p <= 0.f) return 1.f;
-  const float u = (hash_u32(seed, idx) >> 8) * (1.0f / 16777216.0f);
-  return u >= p ? inv_keep : 0.f;
-}
-
 // ------------------------------------------------------------------------------------------
 // z = dropout(x) + residual ; y = LN(z) * gamma + beta.   One warp per row when cols <= 1024,
 // otherwise one block per row.  Saves z (optional), mean and rstd for the backward pass.
@@ -28,13 +21,14 @@ ln_fwd_warp_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
                    const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
                    __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ z_out,
                    float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int cols,
-                   float eps, float p_drop, uint64_t seed) {
+                   float eps, float p_drop, uint64_t seed, const uint64_t* __restrict__ seed_dev) {
+  if (seed_dev != nullptr) seed += *seed_dev * 0xD1B54A32D192ED03ull;
   const int warps_per_block = blockDim.x >> 5;
   const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
   const int nvec = cols >> 3;
-  const float inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f;
+  const DropRng rng = make_drop_rng(seed, p_drop);
   float v[VEC_PER_LANE][8];
   float sum = 0.f;
 #pragma unroll
@@ -50,8 +44,10 @@ ln_fwd_warp_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
         v[i][2 * t + 1] = bf16_hi(w[t]);
       }
       if (p_drop > 0.f) {
+        float ks[8];
+        drop_scale8(rng, off, ks);
 #pragma unroll
-        for (int t = 0; t < 8; ++t) v[i][t] *= dropout_keep_scale(seed, off + t, p_drop, inv_keep);
+        for (int t = 0; t < 8; ++t) v[i][t] *= ks[t];
       }
       if (residual != nullptr) {
         const uint4 r = *reinterpret_cast<const uint4*>(residual + off);
@@ -124,10 +120,11 @@ ln_fwd_block_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
                     const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ beta,
                     __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ z_out,
                     float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int cols,
-                    float eps, float p_drop, uint64_t seed) {
+                    float eps, float p_drop, uint64_t seed, const uint64_t* __restrict__ seed_dev) {
+  if (seed_dev != nullptr) seed += *seed_dev * 0xD1B54A32D192ED03ull;
   __shared__ float scratch[32];
   const int row = blockIdx.x;
-  const float inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f;
+  const DropRng rng = make_drop_rng(seed, p_drop);
   const size_t base = static_cast<size_t>(row) * cols;
   // pass 1: materialise z (into z_out if given, else into y as temporary) and its sum
   __nv_bfloat16* zbuf = z_out != nullptr ? z_out : y;
@@ -139,8 +136,10 @@ ln_fwd_block_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
 #pragma unroll
     for (int t = 0; t < 4; ++t) { v[2 * t] = bf16_lo(w[t]); v[2 * t + 1] = bf16_hi(w[t]); }
     if (p_drop > 0.f) {
+      float ks[8];
+      drop_scale8(rng, base + c, ks);
 #pragma unroll
-      for (int t = 0; t < 8; ++t) v[t] *= dropout_keep_scale(seed, base + c + t, p_drop, inv_keep);
+      for (int t = 0; t < 8; ++t) v[t] *= ks[t];
     }
     if (residual != nullptr) {
       const uint4 r = *reinterpret_cast<const uint4*>(residual + base + c);
@@ -200,14 +199,16 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
               const float* __restrict__ mean, const float* __restrict__ rstd,
               const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ dz_extra,
               __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ dx_drop,
-              float* __restrict__ partial, int rows, int cols, float p_drop, uint64_t seed) {
+              float* __restrict__ partial, int rows, int cols, float p_drop, uint64_t seed,
+              const uint64_t* __restrict__ seed_dev) {
+  if (seed_dev != nullptr) seed += *seed_dev * 0xD1B54A32D192ED03ull;
   extern __shared__ float sm[];  // [2][cols] block-level dgamma/dbeta accumulators
   float* s_dg = sm;
   float* s_db = sm + cols;
   for (int c = threadIdx.x; c < 2 * cols; c += blockDim.x) sm[c] = 0.f;
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  const float inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f;
+  const DropRng rng = make_drop_rng(seed, p_drop);
   const int nvec = cols >> 3;
   constexpr int R = VPL > 0 ? VPL : 1;
   float acc_dg[R][8], acc_db[R][8];
@@ -275,9 +276,10 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
           make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
                      pack_bf16x2(o[6], o[7]));
       if (dx_drop != nullptr) {
+        float ks[8];
+        drop_scale8(rng, base + vi * 8, ks);
 #pragma unroll
-        for (int t = 0; t < 8; ++t)
-          o[t] *= dropout_keep_scale(seed, base + vi * 8 + t, p_drop, inv_keep);
+        for (int t = 0; t < 8; ++t) o[t] *= ks[t];
         *reinterpret_cast<uint4*>(dx_drop + base + vi * 8) =
             make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
                        pack_bf16x2(o[6], o[7]));
@@ -303,33 +305,53 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
 }
 
 // Reduces [nblocks, 2, cols] partials into dgamma/dbeta (bf16 or fp32, optionally accumulating).
-__global__ void ln_bwd_finalize_kernel(const float* __restrict__ partial, int nblocks, int cols,
-                                       void* __restrict__ dgamma, void* __restrict__ dbeta,
-                                       int out_fp32, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= 2 * cols) return;
-  float s = 0.f;
-  for (int b = 0; b < nblocks; ++b) s += partial[static_cast<size_t>(b) * 2 * cols + c];
-  void* dst = c < cols ? dgamma : dbeta;
-  const int i = c < cols ? c : c - cols;
-  if (out_fp32) {
-    float* d = static_cast<float*>(dst);
-    d[i] = accumulate ? d[i] + s : s;
-  } else {
-    __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dst);
-    d[i] = __float2bfloat16(accumulate ? __bfloat162float(d[i]) + s : s);
+// Block = 32 columns x 8 segments of the partial rows; coalesced loads, smem tree at the end.
+__global__ void __launch_bounds__(256)
+ln_bwd_finalize_kernel(const float* __restrict__ partial, int nblocks, int cols,
+                       void* __restrict__ dgamma, void* __restrict__ dbeta, int out_fp32,
+                       int accumulate) {
+  __shared__ float s[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  float a0 = 0.f, a1 = 0.f;
+  if (c < 2 * cols) {
+    int b = ty;
+    for (; b + 8 < nblocks; b += 16) {
+      a0 += partial[static_cast<size_t>(b) * 2 * cols + c];
+      a1 += partial[static_cast<size_t>(b + 8) * 2 * cols + c];
+    }
+    if (b < nblocks) a0 += partial[static_cast<size_t>(b) * 2 * cols + c];
+  }
+  s[ty][tx] = a0 + a1;
+  __syncthreads();
+  if (ty == 0 && c < 2 * cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += s[k][tx];
+    void* dst = c < cols ? dgamma : dbeta;
+    const int i = c < cols ? c : c - cols;
+    if (out_fp32) {
+      float* d = static_cast<float*>(dst);
+      d[i] = accumulate ? d[i] + t : t;
+    } else {
+      __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dst);
+      d[i] = __float2bfloat16(accumulate ? __bfloat162float(d[i]) + t : t);
+    }
   }
 }
 
 // ------------------------------------------------------------------------------------------
 // Column sum of a [rows, cols] bf16 matrix (bias gradients): out[c] = sum_r x[r, c].
 // grid = (cols/64 tiles, row splits); split partials are combined with fp32 atomics when
-// gridDim.y > 1 (caller zeroes `scratch`), then cast by colsum_finalize_kernel.
+// gridDim.y > 1 (caller zeroes `scratch` once); the last-arriving row-split block of each
+// column tile folds the partial sums, writes the result and re-zeroes the scratch: one launch.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 colsum_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, int ld,
-              float* __restrict__ scratch) {
+              float* __restrict__ scratch, unsigned int* __restrict__ counters,
+              void* __restrict__ out, int out_fp32, int accumulate) {
   __shared__ float s[8][64];
+  __shared__ bool is_last;
   const int c0 = blockIdx.x * 64;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 column-pairs x 8 row lanes
   const int c = c0 + tx * 2;
@@ -338,6 +360,7 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, int ld,
   const int r_begin = blockIdx.y * rows_per;
   const int r_end = min(rows, r_begin + rows_per);
   if (c + 1 < cols) {
+#pragma unroll 4
     for (int r = r_begin + ty; r < r_end; r += 8) {
       const uint32_t u = *reinterpret_cast<const uint32_t*>(x + static_cast<size_t>(r) * ld + c);
       a0 += bf16_lo(u);
@@ -350,26 +373,43 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, int ld,
   s[ty][tx * 2] = a0;
   s[ty][tx * 2 + 1] = a1;
   __syncthreads();
+  float t = 0.f;
+  const int cc = c0 + threadIdx.x;
   if (threadIdx.x < 64) {
-    float t = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) t += s[k][threadIdx.x];
-    const int cc = c0 + threadIdx.x;
-    if (cc < cols) atomicAdd(&scratch[cc], t);
   }
-}
-__global__ void colsum_finalize_kernel(float* __restrict__ scratch, void* __restrict__ out,
-                                       int cols, int out_fp32, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
-  const float s = scratch[c];
-  scratch[c] = 0.f;  // leave the scratch zeroed for the next call
-  if (out_fp32) {
-    float* d = static_cast<float*>(out);
-    d[c] = accumulate ? d[c] + s : s;
-  } else {
-    __nv_bfloat16* d = static_cast<__nv_bfloat16*>(out);
-    d[c] = __float2bfloat16(accumulate ? __bfloat162float(d[c]) + s : s);
+  if (gridDim.y == 1) {  // no row split: write the result directly
+    if (threadIdx.x < 64 && cc < cols) {
+      if (out_fp32) {
+        float* d = static_cast<float*>(out);
+        d[cc] = accumulate ? d[cc] + t : t;
+      } else {
+        __nv_bfloat16* d = static_cast<__nv_bfloat16*>(out);
+        d[cc] = __float2bfloat16(accumulate ? __bfloat162float(d[cc]) + t : t);
+      }
+    }
+    return;
+  }
+  if (threadIdx.x < 64 && cc < cols) atomicAdd(&scratch[cc], t);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = (atomicAdd(&counters[blockIdx.x], 1u) == gridDim.y - 1);
+  __syncthreads();
+  if (is_last) {  // the last row-split block of this column tile folds the partial sums
+    __threadfence();
+    if (threadIdx.x < 64 && cc < cols) {
+      const float v = __ldcg(&scratch[cc]);
+      scratch[cc] = 0.f;  // leave the scratch zeroed for the next call
+      if (out_fp32) {
+        float* d = static_cast<float*>(out);
+        d[cc] = accumulate ? d[cc] + v : v;
+      } else {
+        __nv_bfloat16* d = static_cast<__nv_bfloat16*>(out);
+        d[cc] = __float2bfloat16(accumulate ? __bfloat162float(d[cc]) + v : v);
+      }
+    }
+    if (threadIdx.x == 0) counters[blockIdx.x] = 0;
   }
 }
 
@@ -413,17 +453,20 @@ __global__ void act_bwd_kernel(const __nv_bfloat16* __restrict__ dy,
 // y = x * keep_scale(seed, i) (+ residual).  Backward is the same kernel applied to dy.
 __global__ void dropout_kernel(const __nv_bfloat16* __restrict__ x,
                                const __nv_bfloat16* __restrict__ residual,
-                               __nv_bfloat16* __restrict__ y, size_t n, float p, uint64_t seed) {
+                               __nv_bfloat16* __restrict__ y, size_t n, float p, uint64_t seed,
+                               const uint64_t* __restrict__ seed_dev) {
+  if (seed_dev != nullptr) seed += *seed_dev * 0xD1B54A32D192ED03ull;
   const size_t i = (static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 8;
-  const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const DropRng rng = make_drop_rng(seed, p);
   if (i + 8 <= n) {
     const uint4 u = *reinterpret_cast<const uint4*>(x + i);
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-    float v[8];
+    float v[8], ks[8];
 #pragma unroll
     for (int t = 0; t < 4; ++t) { v[2 * t] = bf16_lo(w[t]); v[2 * t + 1] = bf16_hi(w[t]); }
+    drop_scale8(rng, i, ks);
 #pragma unroll
-    for (int t = 0; t < 8; ++t) v[t] *= dropout_keep_scale(seed, i + t, p, inv_keep);
+    for (int t = 0; t < 8; ++t) v[t] *= ks[t];
     if (residual != nullptr) {
       const uint4 r = *reinterpret_cast<const uint4*>(residual + i);
       const uint32_t rw[4] = {r.x, r.y, r.z, r.w};
@@ -435,7 +478,7 @@ __global__ void dropout_kernel(const __nv_bfloat16* __restrict__ x,
                    pack_bf16x2(v[6], v[7]));
   } else {
     for (size_t j = i; j < n; ++j) {
-      float v = __bfloat162float(x[j]) * dropout_keep_scale(seed, j, p, inv_keep);
+      float v = __bfloat162float(x[j]) * drop_scale1(rng, j);
       if (residual != nullptr) v += __bfloat162float(residual[j]);
       y[j] = __float2bfloat16(v);
     }
@@ -497,7 +540,8 @@ using namespace dtds;
 extern "C" int dtds_layernorm_fwd(const void* x, const void* residual, const void* gamma,
                                   const void* beta, void* y, void* z_out, float* mean, float* rstd,
                                   int rows, int cols, float eps, float p_drop,
-                                  unsigned long long seed, cudaStream_t stream) {
+                                  unsigned long long seed, const unsigned long long* seed_dev,
+                                  cudaStream_t stream) {
   if (rows <= 0) return 0;
   if (cols % 8 != 0) {
     fprintf(stderr, "[dtds] layernorm: cols (%d) must be a multiple of 8\n", cols);
@@ -512,13 +556,13 @@ extern "C" int dtds_layernorm_fwd(const void* x, const void* residual, const voi
   const int wpb = 8;
   const int grid = (rows + wpb - 1) / wpb;
   if (cols <= 256) {
-    ln_fwd_warp_kernel<1><<<grid, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed);
+    ln_fwd_warp_kernel<1><<<grid, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev));
   } else if (cols <= 768) {
-    ln_fwd_warp_kernel<3><<<grid, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed);
+    ln_fwd_warp_kernel<3><<<grid, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev));
   } else if (cols <= 1024) {
-    ln_fwd_warp_kernel<4><<<grid, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed);
+    ln_fwd_warp_kernel<4><<<grid, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev));
   } else {
-    ln_fwd_block_kernel<<<rows, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed);
+    ln_fwd_block_kernel<<<rows, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev));
   }
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
@@ -526,8 +570,8 @@ extern "C" int dtds_layernorm_fwd(const void* x, const void* residual, const voi
 
 extern "C" int dtds_layernorm_bwd_blocks(int rows, int cols) {
   (void)cols;
-  int blocks = (rows + 7) / 8;
-  const int cap = 2 * dtds::sm_count();
+  int blocks = (rows + 31) / 32;  // >= 4 rows per warp so the register accumulators pay off
+  const int cap = dtds::sm_count();
   return blocks < cap ? (blocks < 1 ? 1 : blocks) : cap;
 }
 
@@ -535,7 +579,8 @@ extern "C" int dtds_layernorm_bwd(const void* dy, const void* z, const float* me
                                   const float* rstd, const void* gamma, const void* dz_extra,
                                   void* dz, void* dx_drop, void* dgamma, void* dbeta,
                                   float* partial /* [blocks,2,cols] */, int rows, int cols,
-                                  float p_drop, unsigned long long seed, int grads_fp32,
+                                  float p_drop, unsigned long long seed,
+                                  const unsigned long long* seed_dev, int grads_fp32,
                                   int accumulate, cudaStream_t stream) {
   if (rows <= 0) return 0;
   if (cols % 8 != 0) return -1;
@@ -546,7 +591,7 @@ extern "C" int dtds_layernorm_bwd(const void* dy, const void* z, const float* me
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(z), mean, rstd,    \
       static_cast<const __nv_bfloat16*>(gamma), static_cast<const __nv_bfloat16*>(dz_extra),      \
       static_cast<__nv_bfloat16*>(dz), static_cast<__nv_bfloat16*>(dx_drop), partial, rows, cols, \
-      p_drop, seed)
+      p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev))
   if (cols <= 256) DTDS_LN_BWD(1);
   else if (cols <= 768) DTDS_LN_BWD(3);
   else if (cols <= 1024) DTDS_LN_BWD(4);
@@ -560,23 +605,31 @@ extern "C" int dtds_layernorm_bwd(const void* dy, const void* z, const float* me
 #undef DTDS_LN_BWD
   DTDS_HOST_CHECK(cudaGetLastError());
   if (dgamma != nullptr && dbeta != nullptr) {
-    ln_bwd_finalize_kernel<<<(2 * cols + 255) / 256, 256, 0, stream>>>(partial, blocks, cols, dgamma,
-                                                                      dbeta, grads_fp32, accumulate);
+    ln_bwd_finalize_kernel<<<(2 * cols + 31) / 32, 256, 0, stream>>>(partial, blocks, cols, dgamma,
+                                                                     dbeta, grads_fp32, accumulate);
     DTDS_HOST_CHECK(cudaGetLastError());
   }
   return 0;
 }
 
-extern "C" int dtds_colsum(const void* x, int rows, int cols, int ld, float* scratch /* [cols], zeroed */,
+extern "C" int dtds_colsum(const void* x, int rows, int cols, int ld,
+                           float* scratch /* [cols + cols/64 + 130] zeroed once by the caller */,
                            void* out, int out_fp32, int accumulate, cudaStream_t stream) {
   if (rows <= 0 || cols <= 0) return 0;
-  int splits = rows / 256;
-  if (splits < 1) splits = 1;
-  if (splits > 32) splits = 32;
-  dim3 grid((cols + 63) / 64, splits);
-  colsum_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), rows, cols, ld, scratch);
-  DTDS_HOST_CHECK(cudaGetLastError());
-  colsum_finalize_kernel<<<(cols + 255) / 256, 256, 0, stream>>>(scratch, out, cols, out_fp32, accumulate);
+  const int tiles = (cols + 63) / 64;
+  int splits = 1;
+  if (tiles < 2 * dtds::sm_count()) {
+    splits = (2 * dtds::sm_count() + tiles - 1) / tiles;
+    const int max_splits = (rows + 63) / 64;
+    if (splits > max_splits) splits = max_splits;
+    if (splits > 64) splits = 64;
+    if (splits < 1) splits = 1;
+  }
+  dim3 grid(tiles, splits);
+  // per-tile arrival counters live right after the partial sums (same zeroed scratch)
+  unsigned int* counters = reinterpret_cast<unsigned int*>(scratch + tiles * 64);
+  colsum_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), rows, cols, ld, scratch,
+                                          counters, out, out_fp32, accumulate);
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }
@@ -600,12 +653,14 @@ extern "C" int dtds_act_bwd(const void* dy, const void* x, void* dx, size_t n, i
   return 0;
 }
 extern "C" int dtds_dropout(const void* x, const void* residual, void* y, size_t n, float p,
-                            unsigned long long seed, cudaStream_t stream) {
+                            unsigned long long seed, const unsigned long long* seed_dev,
+                            cudaStream_t stream) {
   if (n == 0) return 0;
   const size_t threads = (n + 7) / 8;
   dropout_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(residual),
-      static_cast<__nv_bfloat16*>(y), n, p, seed);
+      static_cast<__nv_bfloat16*>(y), n, p, seed,
+      reinterpret_cast<const uint64_t*>(seed_dev));
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }

@@ -105,9 +105,14 @@ def ptr(t) -> int | None:
     return None if t is None else t.data_ptr()
 
 
+# kernels launched per C call (default 1); used for the launch accounting bench.py reports
+_KERNELS_PER_CALL = {"dtds_cross_entropy": 2, "dtds_layernorm_bwd": 2,
+                     "dtds_attention_bwd": 3, "dtds_adam_flat": 2}
+
+
 def check(rc: int, what: str) -> None:
     global _launches
-    _launches += 1
+    _launches += _KERNELS_PER_CALL.get(what, 1)
     if rc != 0:
         raise NativeLibraryError(f"{what} failed with code {rc} (see stderr for details)")
 

@@ -1,0 +1,394 @@
+"""Autograd wrappers around the sm_100a kernels.
+
+Each ``torch.autograd.Function`` here is one fused forward and one fused backward built from the
+raw kernels in ``kernels.py``; CPU tensors run the same code through the fp32 reference ops, so
+the engines and CLIs can be tested without a GPU.
+
+Gradient emission protocol (used by the DDP / ZeRO engines, see parallel/flat.py): if a
+parameter carries ``main_grad`` (a view into a flat gradient buffer) the weight-gradient GEMM
+writes — or accumulates — straight into it, no ``.grad`` tensor is produced, and the parameter's
+``_on_grad_ready`` callback fires as soon as the kernel is enqueued.  That is what lets the
+bucketed all-reduce / reduce-scatter start while the rest of backward is still running, with no
+pack or unpack copies ("DDP variant writes dW straight into the flat bucket").
+"""
+from __future__ import annotations
+
+import itertools
+import math
+
+import torch
+
+from . import kernels as K
+from .reference import ACT_NONE
+
+_seed_counter = itertools.count(0x5EED)
+_base_seed = 0
+
+
+def manual_seed(seed: int) -> None:
+    """Seeds the dropout streams of the fused kernels (independent of torch's generator)."""
+    global _seed_counter, _base_seed
+    _base_seed = int(seed) & 0xFFFFFFFF
+    _seed_counter = itertools.count(0x5EED)
+
+
+def next_seed() -> int:
+    return ((_base_seed << 32) ^ (next(_seed_counter) * 0x9E3779B1)) & 0x7FFFFFFFFFFFFFFF
+
+
+# ------------------------------------------------------------------ gradient emission helpers
+def grad_target(param):
+    """(buffer, accumulate) for a parameter that owns a flat-buffer gradient view, else (None, _)."""
+    mg = getattr(param, "main_grad", None)
+    if mg is None:
+        return None, False
+    return mg, bool(getattr(param, "_grad_written", False))
+
+
+def grad_done(param) -> None:
+    param._grad_written = True
+    pending = getattr(param, "_uses_pending", 1) - 1
+    param._uses_pending = pending
+    if pending <= 0:
+        cb = getattr(param, "_on_grad_ready", None)
+        if cb is not None:
+            cb(param)
+
+
+def _emit(param, compute):
+    """compute(out, accumulate) -> tensor.  Returns the value autograd should see for `param`."""
+    if param is None or not param.requires_grad:
+        return None
+    mg, acc = grad_target(param)
+    if mg is not None:
+        compute(mg, acc)
+        grad_done(param)
+        return None
+    return compute(None, False)
+
+
+def _wgrad(dy2, x2, param):
+    """dW[N,K] = dy2[M,N]ᵀ · x2[M,K] emitted per the protocol above."""
+    def compute(out, acc):
+        if out is None:
+            return K.gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out_dtype=param.dtype)
+        return K.gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=out, accumulate=acc)
+    return _emit(param, compute)
+
+
+def _bgrad(dy2, param):
+    def compute(out, acc):
+        if out is None:
+            return K.colsum(dy2).to(param.dtype)
+        return K.colsum(dy2, out=out, accumulate=acc)
+    return _emit(param, compute)
+
+
+# ------------------------------------------------------------------------------------ Linear
+class LinearFn(torch.autograd.Function):
+    """y = act(x·Wᵀ + b) (+ residual).  Forward: one GEMM with fused epilogue.  Backward: optional
+    activation backward, dgrad GEMM (W consumed MN-major, no transpose), wgrad GEMM (both operands
+    MN-major) written into the flat gradient buffer, bias column-sum."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, act, residual):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        N = weight.shape[0]
+        need_pre = act != ACT_NONE and any(ctx.needs_input_grad)
+        pre = torch.empty(x2.shape[0], N, dtype=x2.dtype, device=x2.device) if need_pre else None
+        res2 = residual.reshape(-1, N) if residual is not None else None
+        y = K.gemm(x2, weight, bias=bias, act=act, residual=res2, pre_out=pre)
+        ctx.save_for_backward(x2, weight, bias, pre)
+        ctx.act = act
+        ctx.has_res = residual is not None
+        ctx.in_shape = shape
+        return y.view(*shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, bias, pre = ctx.saved_tensors
+        N = weight.shape[0]
+        dy2 = dy.reshape(-1, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dres = dy if ctx.has_res else None
+        du = K.act_bwd(dy2, pre, ctx.act) if ctx.act != ACT_NONE else dy2
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = K.gemm(du, weight, b_mn_major=True).view(ctx.in_shape)
+        dw = _wgrad(du, x2, weight) if ctx.needs_input_grad[1] else None
+        db = _bgrad(du, bias) if (bias is not None and ctx.needs_input_grad[2]) else None
+        return dx, dw, db, None, dres
+
+
+def linear(x, weight, bias=None, act=ACT_NONE, residual=None):
+    return LinearFn.apply(x, weight, bias, act, residual)
+
+
+# --------------------------------------------------------------------------------------- MLP
+class MLPFn(torch.autograd.Function):
+    """f = act(x·W1ᵀ + b1)·W2ᵀ + b2 (+ residual).  The backward of the activation is fused into
+    the epilogue of the W2 dgrad GEMM (du = (df·W2) ⊙ act'(u)); no standalone elementwise pass."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, act, residual):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        M, F = x2.shape[0], w1.shape[0]
+        u = torch.empty(M, F, dtype=x2.dtype, device=x2.device)
+        a = K.gemm(x2, w1, bias=b1, act=act, pre_out=u)
+        res2 = residual.reshape(-1, w2.shape[0]) if residual is not None else None
+        f = K.gemm(a, w2, bias=b2, residual=res2)
+        ctx.save_for_backward(x2, w1, b1, w2, b2, u, a)
+        ctx.act = act
+        ctx.has_res = residual is not None
+        ctx.in_shape = shape
+        return f.view(*shape[:-1], w2.shape[0])
+
+    @staticmethod
+    def backward(ctx, df):
+        x2, w1, b1, w2, b2, u, a = ctx.saved_tensors
+        df2 = df.reshape(-1, w2.shape[0])
+        if not df2.is_contiguous():
+            df2 = df2.contiguous()
+        dres = df if ctx.has_res else None
+        du = K.gemm(df2, w2, b_mn_major=True, act=ctx.act, dact_in=u)
+        dw2 = _wgrad(df2, a, w2)
+        db2 = _bgrad(df2, b2) if b2 is not None else None
+        dx = K.gemm(du, w1, b_mn_major=True).view(ctx.in_shape) if ctx.needs_input_grad[0] else None
+        dw1 = _wgrad(du, x2, w1)
+        db1 = _bgrad(du, b1) if b1 is not None else None
+        return dx, dw1, db1, dw2, db2, None, dres
+
+
+def mlp(x, w1, b1, w2, b2, act, residual=None):
+    return MLPFn.apply(x, w1, b1, w2, b2, act, residual)
+
+
+# --------------------------------------------------------------------------------- LayerNorm
+class LayerNormFn(torch.autograd.Function):
+    """y = LN(dropout(x) + residual).  One kernel forward (dropout mask recomputed from its seed
+    in backward, never stored), one kernel + a tiny finalize backward."""
+
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, eps, p_drop, training):
+        p = p_drop if training else 0.0
+        seed = next_seed() if p > 0.0 else 0
+        y, z, mean, rstd = K.layernorm_fwd(x, residual, gamma, beta, eps, p, seed)
+        ctx.save_for_backward(z, mean, rstd, gamma, beta)
+        ctx.p, ctx.seed = p, seed
+        ctx.has_res = residual is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        z, mean, rstd, gamma, beta = ctx.saved_tensors
+        if not dy.is_contiguous():
+            dy = dy.contiguous()
+        mg_g, acc_g = grad_target(gamma)
+        mg_b, acc_b = grad_target(beta)
+        direct = mg_g is not None and mg_b is not None and acc_g == acc_b
+        dz, dxd, dg, db = K.layernorm_bwd(
+            dy, z, mean, rstd, gamma, p_drop=ctx.p, seed=ctx.seed,
+            dgamma_out=mg_g if direct else None, dbeta_out=mg_b if direct else None,
+            accumulate=acc_g if direct else False, want_dx_drop=True)
+        if direct:
+            grad_done(gamma)
+            grad_done(beta)
+            dg = db = None
+        else:
+            dg = _emit(gamma, lambda out, acc: dg if out is None else (out.add_(dg) if acc else out.copy_(dg)))
+            db = _emit(beta, lambda out, acc: db if out is None else (out.add_(db) if acc else out.copy_(db)))
+        return dxd, (dz if ctx.has_res else None), dg, db, None, None, None
+
+
+def layer_norm(x, gamma, beta, eps=1e-5, residual=None, p_drop=0.0, training=False):
+    return LayerNormFn.apply(x, residual, gamma, beta, eps, p_drop, training)
+
+
+# --------------------------------------------------------------------------------- attention
+class AttentionFn(torch.autograd.Function):
+    """ctx[B*S, H] = softmax(scale·QKᵀ + bias)·V from the fused QKV activations [B*S, 3H]."""
+
+    @staticmethod
+    def forward(ctx, qkv, B, S, heads, scale, causal, key_bias, alibi, p_drop, training):
+        p = p_drop if training else 0.0
+        seed = next_seed() if p > 0.0 else 0
+        out, lse = K.attention_fwd(qkv, B, S, heads, scale=scale, causal=causal, key_bias=key_bias,
+                                   alibi=alibi, p_drop=p, seed=seed)
+        ctx.save_for_backward(qkv, out, lse, key_bias, alibi)
+        ctx.cfg = (B, S, heads, scale, causal, p, seed)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse, key_bias, alibi = ctx.saved_tensors
+        B, S, heads, scale, causal, p, seed = ctx.cfg
+        dqkv = K.attention_bwd(qkv, out, dout, lse, B, S, heads, scale=scale, causal=causal,
+                               key_bias=key_bias, alibi=alibi, p_drop=p, seed=seed)
+        return (dqkv,) + (None,) * 9
+
+
+def attention(qkv, B, S, heads, *, scale=None, causal=False, key_bias=None, alibi=None,
+              p_drop=0.0, training=False):
+    H = qkv.shape[-1] // 3
+    if scale is None:
+        scale = 1.0 / math.sqrt(H // heads)
+    return AttentionFn.apply(qkv, B, S, heads, scale, causal, key_bias, alibi, p_drop, training)
+
+
+# --------------------------------------------------------------------------------- embedding
+class EmbeddingFn(torch.autograd.Function):
+    """word[ids] + pos[0..S) + type[0]: one gather kernel forward; backward = atomic scatter-add
+    into the word table gradient, batch reduction for positions, column sum for the type row."""
+
+    @staticmethod
+    def forward(ctx, ids, word, pos, typ, pos_offset):
+        out = K.embedding_fwd(ids, word, pos, typ, None, pos_offset)
+        ctx.save_for_backward(ids)
+        ctx.params = (word, pos, typ)
+        ctx.pos_offset = pos_offset
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (ids,) = ctx.saved_tensors
+        word, pos, typ = ctx.params
+        B, S = ids.shape
+        H = dout.shape[-1]
+        if not dout.is_contiguous():
+            dout = dout.contiguous()
+
+        def word_compute(out, acc):
+            tgt = out
+            if tgt is None:
+                tgt = torch.zeros_like(word)
+            elif not acc:
+                tgt.zero_()
+            K.embedding_bwd(ids, dout, tgt, None)
+            return tgt
+
+        def pos_compute(out, acc):
+            tgt = out
+            if tgt is None:
+                tgt = torch.zeros_like(pos)
+            elif not acc:
+                tgt.zero_()
+            K.embedding_bwd(ids, dout, None, tgt, pos_offset=ctx.pos_offset, accumulate_pos=True)
+            return tgt
+
+        def type_compute(out, acc):
+            tgt = out
+            if tgt is None:
+                tgt = torch.zeros_like(typ)
+            elif not acc:
+                tgt.zero_()
+            K.colsum(dout.view(B * S, H), out=tgt[0], accumulate=True)
+            return tgt
+
+        dword = _emit(word, word_compute)
+        dpos = _emit(pos, pos_compute) if pos is not None else None
+        dtyp = _emit(typ, type_compute) if typ is not None else None
+        return None, dword, dpos, dtyp, None
+
+
+def embedding(ids, word, pos=None, typ=None, pos_offset=0):
+    return EmbeddingFn.apply(ids, word, pos, typ, pos_offset)
+
+
+# ------------------------------------------------------------------------------------- losses
+class CrossEntropyFn(torch.autograd.Function):
+    """Mean cross-entropy with ignore_index over logits [R, V] (row stride may be padded).
+
+    Forward and backward are one pass over the logits: the gradient is written in place into the
+    logits buffer, so the op needs no second [R, V] tensor.  The upstream gradient is assumed to
+    be the scalar ``gscale`` given at call time (1.0 for a plain ``loss.backward()``)."""
+
+    @staticmethod
+    def forward(ctx, logits2, labels, vocab, ignore_index, shift, seq, gscale):
+        want_grad = ctx.needs_input_grad[0]
+        loss, d = K.cross_entropy(logits2, labels, vocab=vocab, ignore_index=ignore_index,
+                                  shift=shift, seq=seq, want_grad=want_grad, inplace_grad=True,
+                                  gscale=gscale)
+        ctx.d = d
+        return loss.clone()
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        d, ctx.d = ctx.d, None
+        return d, None, None, None, None, None, None
+
+
+def cross_entropy(logits, labels, *, ignore_index=-100, shift=False, gscale=1.0):
+    """logits [..., V] (last dim contiguous; rows may be padded), labels [...] int64."""
+    V = logits.shape[-1]
+    if logits.dim() == 3:
+        seq = logits.shape[1]
+        l2 = logits.reshape(-1, V) if logits.is_contiguous() else \
+            logits.as_strided((logits.shape[0] * seq, V), (logits.stride(1), 1), logits.storage_offset())
+    else:
+        seq = logits.shape[0]
+        l2 = logits
+    if l2.is_cuda and (l2.stride(0) % 8 != 0):
+        pad = (V + 7) // 8 * 8
+        buf = torch.zeros(l2.shape[0], pad, dtype=l2.dtype, device=l2.device)
+        buf[:, :V] = l2
+        l2 = buf[:, :V]
+    return CrossEntropyFn.apply(l2, labels.reshape(-1), V, ignore_index, shift, seq, gscale)
+
+
+class LMHeadLossFn(torch.autograd.Function):
+    """loss = CE(x·Wᵀ + b, labels): vocabulary projection + cross-entropy as one op.  The logits
+    live in one padded [M, ld] buffer that the CE kernel turns into their own gradient in place;
+    backward is then the dgrad / wgrad / bias column-sum of the projection."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, labels, ignore_index, shift, seq, gscale):
+        x2 = x.reshape(-1, x.shape[-1])
+        M, V = x2.shape[0], weight.shape[0]
+        ld = (V + 63) // 64 * 64
+        buf = torch.empty(M, ld, dtype=x2.dtype, device=x2.device)
+        if ld != V:
+            buf[:, V:].zero_()
+        logits = buf[:, :V]
+        K.gemm(x2, weight, bias=bias, out=logits)
+        want_grad = any(ctx.needs_input_grad)
+        loss, d = K.cross_entropy(buf, labels.reshape(-1), vocab=V, ignore_index=ignore_index,
+                                  shift=shift, seq=seq, want_grad=want_grad, inplace_grad=True,
+                                  gscale=gscale)
+        ctx.save_for_backward(x2, weight, bias)
+        ctx.d = d[:, :V] if d is not None else None
+        ctx.in_shape = x.shape
+        return loss.clone()
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        x2, weight, bias = ctx.saved_tensors
+        d, ctx.d = ctx.d, None
+        dx = K.gemm(d, weight, b_mn_major=True).view(ctx.in_shape) if ctx.needs_input_grad[0] else None
+        dw = _wgrad(d, x2, weight)
+        db = _bgrad(d, bias) if bias is not None else None
+        return dx, dw, db, None, None, None, None, None
+
+
+def lm_head_loss(x, weight, bias, labels, *, ignore_index=-100, shift=False, seq=None, gscale=1.0):
+    seq = seq or (x.shape[1] if x.dim() == 3 else x.shape[0])
+    return LMHeadLossFn.apply(x, weight, bias, labels, ignore_index, shift, seq, gscale)
+
+
+class MSEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, target):
+        loss, dx = K.mse(x, target, want_grad=x.requires_grad)
+        ctx.dx = dx
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        dx, ctx.dx = ctx.dx, None
+        return dx, None
+
+
+def mse_loss(x, target):
+    return MSEFn.apply(x, target)

@@ -12,6 +12,20 @@ from . import _lib, reference as ref
 from .reference import ACT_NONE
 
 _scratch: dict = {}
+_seed_dev = None  # optional uint64 device tensor added to every dropout seed (CUDA-graph replays)
+
+
+def set_seed_offset_tensor(t) -> None:
+    """Registers a 1-element int64 CUDA tensor whose value is mixed into every dropout seed on
+    the device.  Bumping it between CUDA-graph replays gives fresh dropout masks per step even
+    though the host-side seeds were frozen at capture time."""
+    global _seed_dev
+    _seed_dev = t
+
+
+def _seed_ptr():
+    return None if _seed_dev is None else _seed_dev.data_ptr()
+
 
 
 def _scratch_f32(device, n: int, tag: str, zero: bool = False) -> torch.Tensor:
@@ -95,7 +109,7 @@ def layernorm_fwd(x, residual, gamma, beta, eps, p_drop=0.0, seed=0, save_z=True
     rc = _lib.lib().dtds_layernorm_fwd(
         x.data_ptr(), _lib.ptr(_c(residual) if residual is not None else None), gamma.data_ptr(),
         beta.data_ptr(), y.data_ptr(), _lib.ptr(z), mean.data_ptr(), rstd.data_ptr(), rows, cols,
-        float(eps), float(p_drop), int(seed), _lib.stream_ptr())
+        float(eps), float(p_drop), int(seed), _seed_ptr(), _lib.stream_ptr())
     _lib.check(rc, "dtds_layernorm_fwd")
     return y, (z if need_z else x), mean, rstd
 
@@ -131,7 +145,8 @@ def layernorm_bwd(dy, z, mean, rstd, gamma, dz_extra=None, p_drop=0.0, seed=0, d
         dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
         _lib.ptr(_c(dz_extra) if dz_extra is not None else None), dz.data_ptr(), _lib.ptr(dxd),
         dgamma_out.data_ptr(), dbeta_out.data_ptr(), partial.data_ptr(), rows, cols, float(p_drop),
-        int(seed), int(dgamma_out.dtype == torch.float32), int(accumulate), _lib.stream_ptr())
+        int(seed), _seed_ptr(), int(dgamma_out.dtype == torch.float32), int(accumulate),
+        _lib.stream_ptr())
     _lib.check(rc, "dtds_layernorm_bwd")
     if want_dx_drop and dxd is None:
         dxd = dz
@@ -154,7 +169,7 @@ def colsum(x, out=None, accumulate=False):
     if out is None:
         out = torch.empty(cols, dtype=x.dtype, device=x.device)
         accumulate = False
-    scratch = _scratch_f32(x.device, cols, "colsum")  # kernel leaves it zeroed after use
+    scratch = _scratch_f32(x.device, cols + cols // 64 + 130, "colsum")  # sums + counters, left zeroed
     rc = _lib.lib().dtds_colsum(x.data_ptr(), rows, cols, x.stride(0), scratch.data_ptr(),
                                 out.data_ptr(), int(out.dtype == torch.float32), int(accumulate),
                                 _lib.stream_ptr())
@@ -193,7 +208,7 @@ def dropout(x, p, seed, residual=None):
     x = _c(x)
     y = torch.empty_like(x)
     _lib.check(_lib.lib().dtds_dropout(x.data_ptr(), _lib.ptr(_c(residual) if residual is not None else None),
-                                       y.data_ptr(), x.numel(), float(p), int(seed),
+                                       y.data_ptr(), x.numel(), float(p), int(seed), _seed_ptr(),
                                        _lib.stream_ptr()), "dtds_dropout")
     return y
 
@@ -289,25 +304,28 @@ def cross_entropy(logits, labels, *, vocab=None, ignore_index=-100, shift=False,
 
     Returns (loss scalar fp32, dlogits or None).  With inplace_grad the gradient overwrites the
     logits buffer (the logits are dead after the loss anyway)."""
-    R, ld = logits.shape
-    vocab = vocab or ld
+    R = logits.shape[0]
+    ld = logits.stride(0)  # rows may be padded: `logits` can be a [R, vocab] view of a wider buffer
+    vocab = vocab or logits.shape[1]
     seq = seq or R
     if not _lib.use_native(logits):
-        lf = logits[:, :vocab].float().detach().requires_grad_(want_grad)
-        loss, _ = ref.cross_entropy(lf, labels.reshape(-1), ignore_index=ignore_index, shift=shift,
-                                    seq=seq)
-        if not want_grad:
-            return loss.detach(), None
-        (g,) = torch.autograd.grad(loss, lf)
-        d = torch.zeros_like(logits)
+        with torch.enable_grad():  # we may be inside an autograd.Function (grad mode off)
+            lf = logits[:, :vocab].float().detach().requires_grad_(want_grad)
+            loss, _ = ref.cross_entropy(lf, labels.reshape(-1), ignore_index=ignore_index, shift=shift,
+                                        seq=seq)
+            if not want_grad:
+                return loss.detach(), None
+            (g,) = torch.autograd.grad(loss, lf)
+        d = torch.zeros(logits.shape, dtype=logits.dtype, device=logits.device)
         d[:, :vocab] = (g * gscale).to(logits.dtype)
         return loss.detach(), d
-    assert logits.stride(1) == 1 and logits.stride(0) == ld
+    assert logits.stride(1) == 1 and ld >= vocab
     labels = _c(labels.reshape(-1))
     stats = torch.empty(2, dtype=torch.float32, device=logits.device)
     d = None
     if want_grad:
-        d = logits if inplace_grad else torch.empty_like(logits)
+        d = logits if inplace_grad else torch.empty_strided(logits.shape, logits.stride(), dtype=logits.dtype,
+                                                            device=logits.device)
     rc = _lib.lib().dtds_cross_entropy(
         logits.data_ptr(), labels.data_ptr(), _lib.ptr(d), stats.data_ptr(), None, R, vocab, ld,
         seq, int(shift), int(ignore_index), float(gscale), _lib.stream_ptr())
@@ -378,7 +396,7 @@ def attention_fwd(qkv, B, S, heads, *, scale, causal=False, key_bias=None, alibi
     rc = _lib.lib().dtds_attention_fwd(
         qkv.data_ptr(), qkv.stride(0), out.data_ptr(), lse.data_ptr(), _lib.ptr(key_bias),
         _lib.ptr(alibi), B, S, heads, d, float(scale), int(causal), float(p_drop), int(seed),
-        _lib.stream_ptr())
+        _seed_ptr(), _lib.stream_ptr())
     _lib.check(rc, "dtds_attention_fwd")
     return out, lse
 
@@ -389,12 +407,13 @@ def attention_bwd(qkv, out, dout, lse, B, S, heads, *, scale, causal=False, key_
     H = qkv.shape[1] // 3
     d = H // heads
     if not _lib.use_native(qkv):
-        qkv_f = qkv.detach().float().requires_grad_(True)
-        q, k, v = _split_qkv(qkv_f, B, S, heads)
-        o, _ = ref.attention(q, k, v, scale=scale, causal=causal, key_bias=key_bias,
-                             alibi_slopes=alibi, p_drop=p_drop, seed=seed)
-        o = o.transpose(1, 2).reshape(B * S, H)
-        (g,) = torch.autograd.grad(o, qkv_f, dout.float())
+        with torch.enable_grad():
+            qkv_f = qkv.detach().float().requires_grad_(True)
+            q, k, v = _split_qkv(qkv_f, B, S, heads)
+            o, _ = ref.attention(q, k, v, scale=scale, causal=causal, key_bias=key_bias,
+                                 alibi_slopes=alibi, p_drop=p_drop, seed=seed)
+            o = o.transpose(1, 2).reshape(B * S, H)
+            (g,) = torch.autograd.grad(o, qkv_f, dout.float())
         return g.to(qkv.dtype)
     dout = _c(dout)
     dqkv = torch.empty(B * S, 3 * H, dtype=qkv.dtype, device=qkv.device)
@@ -402,6 +421,6 @@ def attention_bwd(qkv, out, dout, lse, B, S, heads, *, scale, causal=False, key_
     rc = _lib.lib().dtds_attention_bwd(
         qkv.data_ptr(), qkv.stride(0), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
         delta.data_ptr(), dqkv.data_ptr(), _lib.ptr(key_bias), _lib.ptr(alibi), B, S, heads, d,
-        float(scale), int(causal), float(p_drop), int(seed), _lib.stream_ptr())
+        float(scale), int(causal), float(p_drop), int(seed), _seed_ptr(), _lib.stream_ptr())
     _lib.check(rc, "dtds_attention_bwd")
     return dqkv

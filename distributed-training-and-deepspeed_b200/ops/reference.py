@@ -68,32 +68,36 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
     return d.to(out_dtype)
 
 
+def _mix32(h: torch.Tensor) -> torch.Tensor:
+    """murmur3 fmix32 on int64 tensors holding uint32 values."""
+    m = 0xFFFFFFFF
+    h = h ^ (h >> 16)
+    h = (h * 0x85EBCA6B) & m
+    h = h ^ (h >> 13)
+    h = (h * 0xC2B2AE35) & m
+    h = h ^ (h >> 16)
+    return h
+
+
 def dropout_mask_scale(shape, p: float, seed: int, device) -> torch.Tensor:
-    """Reference dropout keep-scale with the same counter-based hash as csrc/common.cuh."""
+    """Keep-scale tensor (0 or 1/(1-p)) for the counter-based dropout of csrc/common.cuh:
+    16 random bits per element, two elements per 32-bit hash of (seed, element_index / 2)."""
     if p <= 0.0:
         return torch.ones(shape, device=device)
     n = 1
     for s in shape:
         n *= s
+    m = 0xFFFFFFFF
     idx = torch.arange(n, dtype=torch.int64, device=device)
-    mask64 = (1 << 64) - 1
-
-    def mul64(a, c):  # (a * c) mod 2^64 on int64 tensors (two's complement wrap is what we want)
-        return a * c
-
-    def to_signed(c):
-        return c - (1 << 64) if c >= (1 << 63) else c
-
-    def lsr(a, k):  # logical shift right on int64
-        return (a >> k) & ((1 << (64 - k)) - 1)
-
-    z = (idx * to_signed(0x9E3779B97F4A7C15)) + to_signed(seed & mask64)
-    z = mul64(z ^ lsr(z, 30), to_signed(0xBF58476D1CE4E5B9))
-    z = mul64(z ^ lsr(z, 27), to_signed(0x94D049BB133111EB))
-    z = z ^ lsr(z, 31)
-    hi = lsr(z, 32)
-    u = (hi >> 8).float() * (1.0 / 16777216.0)
-    keep = (u >= p).float() / (1.0 - p)
+    pair = idx >> 1
+    seed &= (1 << 64) - 1
+    seed_lo, seed_hi = seed & m, (seed >> 32) & m
+    pair_lo, pair_hi = pair & m, (pair >> 32) & m
+    key = seed_lo ^ _mix32((seed_hi + ((pair_hi * 0x85EBCA77) & m)) & m)
+    bits = _mix32(key ^ ((pair_lo * 0x9E3779B1) & m))
+    u = torch.where((idx & 1) == 1, bits >> 16, bits & 0xFFFF)
+    thr = int(p * 65536.0)
+    keep = (u >= thr).float() / (1.0 - p)
     return keep.view(shape)
 
 

@@ -48,19 +48,20 @@ int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const void* bias,
  *      (ATen kernels behind model/transformer.py:36,43-53; BERT post-LN blocks) ------------- */
 int dtds_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta,
                        void* y, void* z_out, float* mean, float* rstd, int rows, int cols,
-                       float eps, float p_drop, unsigned long long seed, cudaStream_t stream);
+                       float eps, float p_drop, unsigned long long seed,
+                       const unsigned long long* seed_dev, cudaStream_t stream);
 int dtds_layernorm_bwd_blocks(int rows, int cols); /* rows of `partial` the backward needs */
 int dtds_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd,
                        const void* gamma, const void* dz_extra, void* dz, void* dx_drop,
                        void* dgamma, void* dbeta, float* partial, int rows, int cols, float p_drop,
-                       unsigned long long seed, int grads_fp32, int accumulate,
-                       cudaStream_t stream);
+                       unsigned long long seed, const unsigned long long* seed_dev, int grads_fp32,
+                       int accumulate, cudaStream_t stream);
 int dtds_colsum(const void* x, int rows, int cols, int ld, float* scratch, void* out, int out_fp32,
                 int accumulate, cudaStream_t stream);
 int dtds_act_fwd(const void* x, void* y, size_t n, int act, cudaStream_t stream);
 int dtds_act_bwd(const void* dy, const void* x, void* dx, size_t n, int act, cudaStream_t stream);
 int dtds_dropout(const void* x, const void* residual, void* y, size_t n, float p,
-                 unsigned long long seed, cudaStream_t stream);
+                 unsigned long long seed, const unsigned long long* seed_dev, cudaStream_t stream);
 int dtds_softmax_rows(const void* x, const void* dy, void* out, int rows, int cols,
                       cudaStream_t stream);
 int dtds_mse(const void* x, const void* t, void* dx, float* loss, size_t n, float gscale,
@@ -93,12 +94,51 @@ int dtds_cast(const void* src, void* dst, size_t n, int to_bf16, cudaStream_t st
 int dtds_attention_fwd(const void* qkv, int ld_qkv, void* out, float* lse, const float* key_bias,
                        const float* alibi_slopes, int B, int S, int heads, int head_dim,
                        float scale, int causal, float p_drop, unsigned long long seed,
-                       cudaStream_t stream);
+                       const unsigned long long* seed_dev, cudaStream_t stream);
 int dtds_attention_bwd(const void* qkv, int ld_qkv, const void* out, const void* dout,
                        const float* lse, float* delta, void* dqkv, const float* key_bias,
                        const float* alibi_slopes, int B, int S, int heads, int head_dim,
                        float scale, int causal, float p_drop, unsigned long long seed,
-                       cudaStream_t stream);
+                       const unsigned long long* seed_dev, cudaStream_t stream);
+
+/* ---- Symmetric-memory runtime + in-kernel collectives over NVLink peer memory (replaces
+ *      ProcessGroupNCCL/NCCL behind pytorch_allreduce.py:31, the DDP Reducer all-reduce behind
+ *      data_parallel_training.py:44, and DeepSpeed ZeRO's reduce/all-gather/FusedAdam sequence
+ *      behind zero_dp_training.py:46-50,88-90) ------------------------------------------------
+ * Every rank allocates the same sizes in the same order; buffers are exported with CUDA IPC and
+ * mapped by all peers.  `data_ptrs` / `signal_ptrs` are host arrays of `world` device addresses
+ * (entry i = rank i's buffer / signal pad as mapped in THIS process).  Every rank must make the
+ * same call with the same sizes; kernels spin on peer flags (bounded; a stuck wait traps).     */
+int dtds_symm_alloc(size_t bytes, unsigned long long* out_ptr);          /* zero-filled       */
+int dtds_symm_free(unsigned long long ptr);
+int dtds_symm_export(unsigned long long ptr, void* handle_out);          /* 64-byte IPC handle */
+int dtds_symm_import(const void* handle, unsigned long long* out_ptr);
+int dtds_symm_close(unsigned long long ptr);
+size_t dtds_signal_pad_bytes(void);
+/* dtype: 0 bf16, 1 fp32, 2 int64 (sum).  algo: 0 auto, 1 one-shot (needs `out` outside the
+ * symmetric buffer), 2 two-shot (in place, out = NULL).  `scale` is applied once to the sum.   */
+int dtds_allreduce(const unsigned long long* data_ptrs, const unsigned long long* signal_ptrs,
+                   int rank, int world, void* out, size_t off_bytes, size_t nbytes, int dtype,
+                   float scale, int algo, int blocks, cudaStream_t stream);
+int dtds_reduce_scatter(const unsigned long long* data_ptrs, const unsigned long long* signal_ptrs,
+                        int rank, int world, void* out, size_t off_bytes, size_t nbytes_per_rank,
+                        int dtype, float scale, int blocks, cudaStream_t stream);
+int dtds_all_gather(const unsigned long long* data_ptrs, const unsigned long long* signal_ptrs,
+                    int rank, int world, const void* in, size_t off_bytes, size_t nbytes_per_rank,
+                    int blocks, cudaStream_t stream);
+int dtds_broadcast(const unsigned long long* data_ptrs, const unsigned long long* signal_ptrs,
+                   int rank, int world, int root, size_t off_bytes, size_t nbytes, int blocks,
+                   cudaStream_t stream);
+int dtds_device_barrier(const unsigned long long* signal_ptrs, int rank, int world,
+                        cudaStream_t stream);
+/* ZeRO step in ONE kernel: reduce-scatter of bf16 gradients + Adam on the owned fp32 partition +
+ * all-gather (push) of the updated bf16 parameters.  Offsets / sizes in elements, multiples of 8. */
+int dtds_zero_step(const unsigned long long* grad_ptrs, const unsigned long long* signal_ptrs,
+                   const unsigned long long* param_ptrs, int rank, int world, size_t goff_elems,
+                   size_t poff_elems, size_t per_rank_elems, float* master, float* m, float* v,
+                   void* param_shard, const int* step, float lr, float beta1, float beta2, float eps,
+                   float weight_decay, float grad_scale, int adamw_mode, int bias_correction,
+                   int push_params, int blocks, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,102 @@
+"""End-to-end checks of the fused models on the GPU: bf16 native kernels vs the fp32 reference
+path of the same modules, and whole-step CUDA-graph capture."""
+import copy
+
+import pytest
+import torch
+
+from dtds_b200.models import build_model, get_config
+from dtds_b200.ops import _lib
+from dtds_b200.optim import FusedAdam
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(name, **over):
+    torch.manual_seed(0)
+    cfg = get_config(name).replace(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0, **over)
+    ref = build_model(cfg).float()
+    gpu = copy.deepcopy(ref).to(device="cuda", dtype=torch.bfloat16)
+    with torch.no_grad():  # make the fp32 reference use exactly the bf16-rounded weights
+        for pr, pg in zip(ref.parameters(), gpu.parameters()):
+            pr.copy_(pg.float().cpu())
+    return cfg, ref, gpu
+
+
+@pytest.mark.parametrize("name", ["bert-tiny", "bloom-tiny", "opt-tiny"])
+def test_model_matches_fp32_reference(name):
+    cfg, ref, gpu = _pair(name)
+    B, S = 2, 128
+    ids = torch.randint(0, cfg.vocab_size, (B, S))
+    labels = ids.clone()
+    if cfg.arch == "bert":
+        labels[:, ::3] = -100
+    lr = ref(ids, labels=labels).loss
+    lr.backward()
+    n0 = _lib.launch_count()
+    lg = gpu(ids.cuda(), labels=labels.cuda()).loss
+    lg.backward()
+    torch.cuda.synchronize()
+    assert _lib.launch_count() > n0, "native kernels were not used"
+    assert abs(lg.item() - lr.item()) < 3e-2 * max(1.0, abs(lr.item())), (lg.item(), lr.item())
+    worst = 0.0
+    for (n, pr), pg in zip(ref.named_parameters(), gpu.parameters()):
+        assert pg.grad is not None, n
+        gr, gg = pr.grad.float(), pg.grad.float().cpu()
+        denom = gr.abs().max().item() + 1e-6
+        rel = (gr - gg).abs().max().item() / denom
+        worst = max(worst, rel)
+        cos = torch.nn.functional.cosine_similarity(gr.flatten(), gg.flatten(), dim=0).item()
+        # ReLU/GELU kinks turn bf16 rounding of pre-activations into a few percent of gradient noise
+        # (the fp32-vs-bf16 CPU reference shows the same), so check direction tightly, magnitude loosely
+        assert cos > 0.995 and rel < 0.25, f"{n}: rel grad err {rel:.3f} cos {cos:.4f} (ref max {denom:.3g})"
+    print("worst relative grad error", worst)
+
+
+def test_logits_path_and_padded_vocab():
+    cfg, ref, gpu = _pair("bert-tiny", vocab_size=1003)  # not a multiple of 8 -> padded rows
+    ids = torch.randint(0, cfg.vocab_size, (2, 128))
+    lo_r = ref(ids).logits
+    lo_g = gpu(ids.cuda()).logits
+    assert lo_g.shape == lo_r.shape
+    err = (lo_g.float().cpu() - lo_r).abs().max().item()
+    assert err < 0.05 * lo_r.abs().max().item() + 0.05, err
+    # loss outside the model, as model_parallel_training.py:73 does
+    labels = ids.clone().cuda()
+    from dtds_b200.ops import functional as Fn
+    out = gpu(ids.cuda()).logits
+    loss = Fn.cross_entropy(out, labels)
+    loss.backward()
+    ref_loss = torch.nn.functional.cross_entropy(lo_r.view(-1, cfg.vocab_size), ids.view(-1))
+    assert abs(loss.item() - ref_loss.item()) < 0.05
+
+
+def test_graphed_step_trains_and_matches_eager():
+    from dtds_b200.parallel.graph import GraphedStep
+    cfg, _, gpu = _pair("bert-tiny")
+    eager = copy.deepcopy(gpu)
+    B, S = 4, 128
+    ids = torch.randint(0, cfg.vocab_size, (B, S), device="cuda")
+    labels = ids.clone()
+    labels[:, ::2] = -100
+
+    def make_step(model, opt):
+        def step(i, l):
+            opt.zero_grad()
+            loss = model(i, labels=l).loss
+            loss.backward()
+            opt.step()
+            return loss
+        return step
+
+    opt_e = FusedAdam(eager.parameters(), lr=2e-3)
+    step_e = make_step(eager, opt_e)
+    ref_losses = [step_e(ids, labels).item() for _ in range(8)]
+
+    opt_g = FusedAdam(gpu.parameters(), lr=2e-3)
+    gs = GraphedStep(make_step(gpu, opt_g), [ids, labels], warmup=3)
+    # warm-up (3) + capture (no execution) consumed optimizer steps: replays continue from step 3
+    losses = [gs(ids, labels).item() for _ in range(5)]
+    assert losses[-1] < losses[0]
+    for a, b in zip(losses, ref_losses[3:]):
+        assert abs(a - b) < 0.05 * max(1.0, abs(b)), (losses, ref_losses)
