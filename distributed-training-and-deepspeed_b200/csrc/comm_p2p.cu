@@ -525,3 +525,62 @@ extern "C" int dtds_zero_step(const unsigned long long* grad_ptrs,
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------- segment gather (pull)
+// ZeRO-3 parameter all-gather as a PULL: each rank copies the slices it needs straight out of the
+// owners' shard buffers (peer loads over NVLink) into a private destination.  No barrier is
+// needed: a shard is only rewritten by the owner's ZeRO step kernel, whose entry barrier cannot
+// pass before every rank has issued (in stream order) all of its gathers of the current step, and
+// whose exit barrier has completed before any rank starts gathering for the next step.
+namespace dtds {
+constexpr int kMaxSegs = 48;
+struct SegArgs {
+  const char* src[kMaxSegs];
+  char* dst[kMaxSegs];
+  unsigned long long nvec[kMaxSegs];  // 16-byte vectors per segment
+  int nseg;
+};
+__global__ void __launch_bounds__(kCommThreads) copy_segments_kernel(SegArgs a) {
+  for (int s = 0; s < a.nseg; ++s) {
+    const char* src = a.src[s];
+    char* dst = a.dst[s];
+    const size_t n = a.nvec[s];
+    for (size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < n;
+         v += static_cast<size_t>(gridDim.x) * blockDim.x)
+      *reinterpret_cast<uint4*>(dst + v * 16) = ld_peer_v4(src + v * 16);
+  }
+}
+}  // namespace dtds
+
+extern "C" int dtds_copy_segments(const unsigned long long* src_ptrs,
+                                  const unsigned long long* dst_ptrs,
+                                  const unsigned long long* nbytes, int nseg, int blocks,
+                                  cudaStream_t stream) {
+  int done = 0;
+  while (done < nseg) {
+    dtds::SegArgs a;
+    memset(&a, 0, sizeof(a));
+    size_t total_vec = 0;
+    int k = 0;
+    for (; k < dtds::kMaxSegs && done + k < nseg; ++k) {
+      if ((nbytes[done + k] % 16) || (src_ptrs[done + k] % 16) || (dst_ptrs[done + k] % 16)) {
+        fprintf(stderr, "[dtds] copy_segments: segments must be 16-byte aligned\n");
+        return -2;
+      }
+      a.src[k] = reinterpret_cast<const char*>(src_ptrs[done + k]);
+      a.dst[k] = reinterpret_cast<char*>(dst_ptrs[done + k]);
+      a.nvec[k] = nbytes[done + k] / 16;
+      total_vec += a.nvec[k];
+    }
+    a.nseg = k;
+    if (total_vec > 0) {
+      int nb = blocks > 0 ? blocks : 64;
+      const size_t need = (total_vec + dtds::kCommThreads - 1) / dtds::kCommThreads;
+      if (need < static_cast<size_t>(nb)) nb = static_cast<int>(need);
+      dtds::copy_segments_kernel<<<nb, dtds::kCommThreads, 0, stream>>>(a);
+      DTDS_HOST_CHECK(cudaGetLastError());
+    }
+    done += k;
+  }
+  return 0;
+}

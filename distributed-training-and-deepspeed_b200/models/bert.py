@@ -94,8 +94,13 @@ class BertOnlyMLMHead(nn.Module):
     def hidden(self, x):
         return self.ln(self.transform(x))
 
-    def forward(self, x):
-        """Returns logits [B, S, V] (a view into a buffer whose rows are padded to 64 columns)."""
+    def forward(self, x, labels=None, ignore_index=-100, gscale=1.0):
+        """Without labels: logits [B, S, V] (a view into a buffer whose rows are padded to 64
+        columns).  With labels: the fused projection + cross-entropy loss (no logits tensor is
+        returned).  Both go through ``__call__`` so module hooks (ZeRO-3 materialisation, idle
+        tracking) see every use of the head's parameters."""
+        if labels is not None:
+            return self.loss(x, labels, ignore_index, gscale)
         t = self.hidden(x)
         B, S, H = t.shape
         V = self.cfg.vocab_size
@@ -166,7 +171,7 @@ class BertForMaskedLM(nn.Module):
         for layer in self.encoders:
             h = layer(h, kb)
         if labels is not None and not return_logits:
-            return MaskedLMOutput(loss=self.head.loss(h, labels))
+            return MaskedLMOutput(loss=self.head(h, labels=labels))
         logits = self.head(h)
         loss = Fn.cross_entropy(logits, labels) if labels is not None else None
         return MaskedLMOutput(loss=loss, logits=logits)

@@ -70,6 +70,8 @@ class FlatBuffers:
                 if with_grads:
                     p.main_grad = self.grad_flat[o:o + p.numel()].view(p.shape)
                 p._flat_owner = self
+                p._orig_shape = tuple(p.shape)
+                p._numel = p.numel()
                 p._flat_offset = o
                 p._grad_written = False
                 p._uses_pending = getattr(p, "_grad_uses", 1)

@@ -1,0 +1,190 @@
+"""Layer-split model parallelism and GPipe pipeline parallelism, one process per stage.
+
+The reference places contiguous module groups on several GPUs inside ONE process, hops
+activations with ``tensor.to(device)`` (model/bert_mp.py:39-47,91-99) and wraps the same modules in
+``torch.distributed.pipeline.sync.Pipe`` for GPipe (model/bert_mp.py:73-89).  Here every stage is
+its own rank and the activation / gradient hand-off between neighbours is NCCL point-to-point
+(``isend`` / ``irecv`` on NCCL's own streams), posted ahead of the compute that needs it so the
+transfer of micro-batch k+1 overlaps the compute of micro-batch k.
+
+Schedule (GPipe, synchronous): all forward micro-batches, then all backward micro-batches in
+reverse order; gradients accumulate across micro-batches; ONE optimizer step per batch.
+``chunks=1`` is the naive model-parallel case: exactly one stage is busy at any time, which is
+what the idle-time table demonstrates.  ``checkpoint='except_last'`` recomputes the forward of all
+micro-batches but the last during backward, like ``Pipe``'s default.
+
+Device idle time is measured on the device: CUDA events bracket every forward/backward segment
+of a stage; the gap between the end of one segment and the start of the next is idle time
+(the reference stamps host ``time.time()`` in hooks without synchronising — quirk Q7).
+"""
+from __future__ import annotations
+
+import time
+
+import torch
+import torch.distributed as dist
+from torch.utils.checkpoint import checkpoint as _checkpoint
+
+
+def split_sizes(n_items: int, n_groups: int) -> list[int]:
+    """Group sizes of ``np.array_split(range(n_items), n_groups)``: the first ``n % k`` groups get
+    one extra item (14 modules -> 2: 7/7, 3: 5/5/4, 4: 4/4/3/3, 8: 2,2,2,2,2,2,1,1)."""
+    base, extra = divmod(n_items, n_groups)
+    return [base + (1 if i < extra else 0) for i in range(n_groups)]
+
+
+def split_ranges(n_items: int, n_groups: int) -> list[range]:
+    out, start = [], 0
+    for s in split_sizes(n_items, n_groups):
+        out.append(range(start, start + s))
+        start += s
+    return out
+
+
+class IdleTracker:
+    """Per-device idle time: sum of gaps between consecutive busy segments."""
+
+    def __init__(self, device: torch.device, verbose: bool = False, log=None):
+        self.device = device
+        self.cuda = device.type == "cuda"
+        self.verbose = verbose
+        self.log = log or (lambda m: None)
+        self._segments = []  # (start, end, label): CUDA events or host timestamps
+        self._open = None
+
+    def enter(self, label: str):
+        if self.cuda:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(torch.cuda.current_stream(self.device))
+        else:
+            ev = time.perf_counter()
+        self._open = (ev, label)
+        if self.verbose:
+            self.log(f"Entering {label} on device {self._dev_index()}")
+
+    def leave(self):
+        if self._open is None:
+            return
+        start, label = self._open
+        if self.cuda:
+            end = torch.cuda.Event(enable_timing=True)
+            end.record(torch.cuda.current_stream(self.device))
+        else:
+            end = time.perf_counter()
+        self._segments.append((start, end, label))
+        self._open = None
+        if self.verbose:
+            self.log(f"Finished {label} on device {self._dev_index()}")
+
+    def _dev_index(self):
+        return self.device.index if self.cuda else 0
+
+    def totals(self) -> tuple[float, int]:
+        """(total idle milliseconds, number of gaps) over everything recorded so far."""
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
+        idle, n = 0.0, 0
+        for (s0, e0, _), (s1, e1, _) in zip(self._segments, self._segments[1:]):
+            gap = e0.elapsed_time(s1) if self.cuda else (s1 - e0) * 1e3
+            idle += max(gap, 0.0)
+            n += 1
+        return idle, n
+
+    def reset(self):
+        self._segments.clear()
+        self._open = None
+
+
+class PipelineStage:
+    """One pipeline stage living in this process."""
+
+    def __init__(self, modules, stage: int, num_stages: int, device: torch.device, *, act_dtype,
+                 group=None, chunks: int = 1, checkpoint: str = "except_last",
+                 tracker: IdleTracker | None = None):
+        self.modules = list(modules)
+        self.stage, self.num_stages = stage, num_stages
+        self.device, self.act_dtype = device, act_dtype
+        self.group = group
+        self.chunks = chunks
+        self.checkpoint = checkpoint
+        self.tracker = tracker or IdleTracker(device)
+        self.is_first, self.is_last = stage == 0, stage == num_stages - 1
+
+    # ------------------------------------------------------------------------------------
+    def _run(self, x):
+        for m in self.modules:
+            x = m(x)
+        return x
+
+    def _forward(self, x, mb: int, n_mb: int):
+        recompute = self.checkpoint == "always" or (self.checkpoint == "except_last" and mb < n_mb - 1)
+        if recompute and n_mb > 1 and torch.is_grad_enabled() and not self.is_first:
+            return _checkpoint(self._run, x, use_reentrant=False)
+        return self._run(x)
+
+    def _irecv(self, shape, src):
+        buf = torch.empty(shape, dtype=self.act_dtype, device=self.device)
+        return buf, dist.irecv(buf, src=src, group=self.group)
+
+    def forward_backward(self, input_ids, labels, act_shape, loss_fn):
+        """One GPipe batch.  `input_ids` is consumed by the first stage, `labels` by the last;
+        `act_shape` = (batch, seq, hidden) of the full batch at stage boundaries;
+        `loss_fn(stage_output, labels_mb, weight)` -> scalar micro-batch loss already scaled so
+        that the micro-batch losses sum to the full-batch loss.  Returns that sum on the last
+        stage, None elsewhere."""
+        M = self.chunks
+        B = act_shape[0]
+        assert B % M == 0, f"batch {B} is not divisible into {M} micro-batches"
+        mb_shape = (B // M,) + tuple(act_shape[1:])
+        prev_rank, next_rank = self.stage - 1, self.stage + 1
+        tr = self.tracker
+        inputs, outputs, losses, sends = [], [], [], []
+        ids_mb = input_ids.chunk(M) if self.is_first else [None] * M
+        lab_mb = labels.chunk(M) if self.is_last else [None] * M
+        if self.is_last:
+            valid = [(l != -100).sum().item() for l in lab_mb]  # labels arrive from the host loader
+            total_valid = max(sum(valid), 1)
+        # ---------------- forward: all micro-batches
+        pending = self._irecv(mb_shape, prev_rank) if not self.is_first else None
+        for k in range(M):
+            if self.is_first:
+                x = ids_mb[k].to(self.device, non_blocking=True)
+            else:
+                buf, work = pending
+                work.wait()
+                pending = self._irecv(mb_shape, prev_rank) if k + 1 < M else None  # overlaps compute
+                x = buf.requires_grad_(True)
+            tr.enter(f"forward pass (micro-batch {k})")
+            y = self._forward(x, k, M)
+            if self.is_last:
+                w = valid[k] / total_valid
+                losses.append(loss_fn(y, lab_mb[k].to(self.device, non_blocking=True), w))
+            tr.leave()
+            inputs.append(x)
+            if self.is_last:
+                outputs.append(None)
+            else:
+                outputs.append(y)
+                sends.append(dist.isend(y.detach(), dst=next_rank, group=self.group))
+        # ---------------- backward: reverse order
+        pending = self._irecv(mb_shape, next_rank) if not self.is_last else None
+        for k in reversed(range(M)):
+            if self.is_last:
+                tr.enter(f"backward pass (micro-batch {k})")
+                losses[k].backward()
+                tr.leave()
+            else:
+                gbuf, work = pending
+                work.wait()
+                pending = self._irecv(mb_shape, next_rank) if k > 0 else None
+                tr.enter(f"backward pass (micro-batch {k})")
+                outputs[k].backward(gbuf)
+                tr.leave()
+            if not self.is_first:
+                sends.append(dist.isend(inputs[k].grad, dst=prev_rank, group=self.group))
+            outputs[k] = None
+        for w in sends:
+            w.wait()
+        if self.is_last:
+            return torch.stack([l.detach() for l in losses]).sum()
+        return None

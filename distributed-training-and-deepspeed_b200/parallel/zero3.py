@@ -1,0 +1,229 @@
+"""ZeRO stage 3: parameter sharding with just-in-time materialisation.
+
+What DeepSpeed's ``partition_parameters`` / ``partitioned_param_coordinator`` do for the
+reference (zero_dp_training.py ``--stage 3``), re-designed for NVSwitch:
+
+  * between uses a rank keeps only its 1/n slice of every bucket ("shard"), in a symmetric buffer
+    that every peer maps;
+  * parameters are materialised per *block* (each element of a ``ModuleList`` — one transformer
+    layer — plus the remaining children of the root): a pre-forward hook pulls the block's slices
+    straight out of the owners' shard buffers over NVLink (one ``copy_segments`` launch, peer
+    loads, no barrier, no staging all-gather buffer on the owner side), a post-forward hook drops
+    them; the same happens around the block's backward.  The next block is prefetched on a side
+    stream while the current one computes;
+  * parameters used by several blocks (tied embeddings) stay materialised for the whole step;
+  * after a block's backward its bucket runs the fused reduce-scatter + Adam kernel, which writes
+    the updated bf16 slice into the owner's shard (no all-gather at all in stage 3).
+
+On CPU/gloo or ``DTDS_COMM=nccl`` materialisation uses ``all_gather_into_tensor`` on the shards.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+from torch import nn
+
+from .. import comm
+from ..ops import _lib
+
+
+class _Block:
+    __slots__ = ("name", "module", "params", "buckets", "live", "event")
+
+    def __init__(self, name, module, params):
+        self.name, self.module, self.params = name, module, params
+        self.buckets, self.live, self.event = [], False, None
+
+
+class Zero3ParamManager:
+    def __init__(self, engine):
+        self.e = engine
+        f = engine.flat
+        self.flat = f
+        self.dev = engine.device
+        self.world, self.rank = engine.world, engine.rank
+        total_own = sum(b.per for b in engine.buckets)
+        esz = f.param_flat.element_size()
+        self.custom = engine._custom and self.world > 1
+        if self.custom:
+            ctx = comm.symm_context(engine.group)
+            self.shard_buf = ctx.new_buffer(total_own * esz)
+            self.shards = self.shard_buf.tensor(f.param_dtype, total_own)
+        else:
+            self.shard_buf = None
+            self.shards = torch.empty(total_own, dtype=f.param_dtype, device=self.dev)
+        self.refresh_shards_from_full()
+        # ---- blocks
+        root = engine.module
+        self.blocks: list[_Block] = []
+        claimed = set()
+        pinned = [p for p in f.params if getattr(p, "_grad_uses", 1) > 1]
+        claimed.update(id(p) for p in pinned)
+
+        def add(name, mod):
+            ps = [p for p in mod.parameters() if id(p) not in claimed and p.requires_grad]
+            if ps:
+                claimed.update(id(p) for p in ps)
+                self.blocks.append(_Block(name, mod, ps))
+
+        for cname, child in root.named_children():
+            if isinstance(child, nn.ModuleList):
+                for i, sub in enumerate(child):
+                    add(f"{cname}.{i}", sub)
+            else:
+                add(cname, child)
+        rest = [p for p in f.params if id(p) not in claimed]
+        self.pinned = _Block("<root>", root, pinned + rest)
+        bucket_of = engine._bucket_of
+        for blk in self.blocks + [self.pinned]:
+            seen = {}
+            for p in blk.params:
+                b = bucket_of[id(p)]
+                seen[b.index] = b
+            blk.buckets = list(seen.values())
+        # ---- release the full replica: from here on parameters point at per-block gather buffers
+        self._full_released = False
+        self._side = torch.cuda.Stream(self.dev) if self.dev.type == "cuda" else None
+        self._order: list[_Block] = []
+        self._placeholder = torch.empty(0, dtype=f.param_dtype, device=self.dev)
+        self._release_full_replica()
+        for i, blk in enumerate(self.blocks):
+            blk.module.register_forward_pre_hook(self._pre(blk, i, +1))
+            blk.module.register_forward_hook(self._post(blk))
+            blk.module.register_full_backward_pre_hook(self._pre_bwd(blk, i))
+            blk.module.register_full_backward_hook(self._post_bwd(blk))
+        root.register_forward_pre_hook(lambda m, a: self._materialize(self.pinned))
+        if self.dev.type == "cuda":
+            torch.cuda.synchronize(self.dev)
+        if self.world > 1:
+            comm.barrier(engine.group)  # every rank's shards are in place before anyone pulls
+
+    # ------------------------------------------------------------------------------------
+    def shard_view(self, b) -> torch.Tensor:
+        return self.shards[b.state_off:b.state_off + b.per]
+
+    def refresh_shards_from_full(self) -> None:
+        f = self.flat
+        for b in self.e.buckets:
+            s = b.lo + self.rank * b.per
+            self.shard_view(b).copy_(f.param_flat[s:s + b.per])
+
+    def _release_full_replica(self) -> None:
+        """Drops the full parameter buffer; every parameter becomes a zero-size placeholder until
+        its block is materialised.  This is where the 1/n parameter memory comes from."""
+        f = self.flat
+        for p in f.params:
+            p.data = self._placeholder
+        f.param_flat = None
+        f.param_buf = None
+        self._full_released = True
+        if self.dev.type == "cuda":
+            torch.cuda.empty_cache()
+
+    def resident_parameter_bytes(self) -> int:
+        """Bytes of parameter storage this rank holds between steps (its shards only)."""
+        return self.shards.numel() * self.shards.element_size()
+
+    # ------------------------------------------------------------------------------------
+    def _gather_bucket(self, b) -> torch.Tensor:
+        """Full copy of bucket `b` assembled from all ranks' shards (transient)."""
+        f = self.flat
+        n = b.hi - b.lo
+        full = torch.empty(n, dtype=self.shards.dtype, device=self.dev)
+        esz = full.element_size()
+        if self.world == 1:
+            full.copy_(self.shard_view(b))
+        elif self.custom:
+            L = _lib.lib()
+            srcs = (ctypes.c_ulonglong * self.world)(*[self.shard_buf.ptrs[r] + b.state_off * esz
+                                                       for r in range(self.world)])
+            dsts = (ctypes.c_ulonglong * self.world)(*[full.data_ptr() + r * b.per * esz
+                                                       for r in range(self.world)])
+            sizes = (ctypes.c_ulonglong * self.world)(*[b.per * esz] * self.world)
+            with comm.comms_logger.record("all_gather(pull)", n * esz, self.world, full):
+                _lib.check(L.dtds_copy_segments(srcs, dsts, sizes, self.world, 0, _lib.stream_ptr()),
+                           "dtds_copy_segments")
+        else:
+            comm.all_gather_into_tensor(full, self.shard_view(b).contiguous(), group=self.e.group)
+        return full
+
+    def _materialize(self, blk: _Block, stream=None) -> None:
+        if blk.live:
+            if blk.event is not None:  # prefetched on the side stream: order it before our use
+                torch.cuda.current_stream(self.dev).wait_event(blk.event)
+                blk.event = None
+            return
+        ctx = torch.cuda.stream(stream) if stream is not None else _Null()
+        with ctx:
+            fulls = {b.index: self._gather_bucket(b) for b in blk.buckets}
+        for p in blk.params:
+            b = self.e._bucket_of[id(p)]
+            o = p._flat_offset - b.lo
+            p.data = fulls[b.index][o:o + p._numel].view(p._orig_shape)
+        if stream is not None:
+            blk.event = torch.cuda.Event()
+            blk.event.record(stream)
+            for t in fulls.values():  # buffers allocated on the side stream, used on the main one
+                t.record_stream(torch.cuda.current_stream(self.dev))
+        blk.live = True
+
+    def _release(self, blk: _Block) -> None:
+        if not blk.live or blk is self.pinned:
+            return
+        for p in blk.params:
+            p.data = self._placeholder
+        blk.live = False
+        blk.event = None
+
+    def _prefetch(self, idx: int) -> None:
+        if self._side is None or not self.e.overlap_comm or not (0 <= idx < len(self.blocks)):
+            return
+        blk = self.blocks[idx]
+        if blk.live:
+            return
+        self._side.wait_stream(torch.cuda.current_stream(self.dev))
+        self._materialize(blk, stream=self._side)
+
+    # hooks ------------------------------------------------------------------------------
+    def _pre(self, blk, idx, direction):
+        def hook(module, args):
+            self._materialize(blk)
+            self._prefetch(idx + direction)
+        return hook
+
+    def _post(self, blk):
+        def hook(module, args, output):
+            self._release(blk)
+        return hook
+
+    def _pre_bwd(self, blk, idx):
+        def hook(module, grad_output):
+            self._materialize(blk)
+            self._prefetch(idx - 1)
+        return hook
+
+    def _post_bwd(self, blk):
+        def hook(module, grad_input, grad_output):
+            self._release(blk)
+        return hook
+
+    def release_all(self) -> None:
+        for blk in self.blocks:
+            self._release(blk)
+        for p in self.pinned.params:
+            p.data = self._placeholder
+        self.pinned.live = False
+
+    def gather_all(self) -> None:
+        """Materialises every parameter (checkpoint export / evaluation outside the engine)."""
+        for blk in self.blocks + [self.pinned]:
+            self._materialize(blk)
+
+
+class _Null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False

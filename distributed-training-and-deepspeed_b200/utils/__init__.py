@@ -1,0 +1,5 @@
+"""Utilities: device probes and size formatting (util.py of the reference), synthetic
+wikitext-shaped datasets, memory telemetry, checkpointing."""
+from .devices import format_size, get_device, get_device_count  # noqa: F401
+from .data import SyntheticTextDataset, load_wikitext  # noqa: F401
+from .memory import memory_status  # noqa: F401

@@ -139,6 +139,10 @@ int dtds_zero_step(const unsigned long long* grad_ptrs, const unsigned long long
                    void* param_shard, const int* step, float lr, float beta1, float beta2, float eps,
                    float weight_decay, float grad_scale, int adamw_mode, int bias_correction,
                    int push_params, int blocks, cudaStream_t stream);
+/* Pull-style gather: copies `nseg` byte ranges (local or peer sources) into local destinations in
+ * one launch; ZeRO-3 uses it to materialise a block's parameters from the owners' shards.      */
+int dtds_copy_segments(const unsigned long long* src_ptrs, const unsigned long long* dst_ptrs,
+                       const unsigned long long* nbytes, int nseg, int blocks, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

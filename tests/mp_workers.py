@@ -1,0 +1,284 @@
+"""Functions executed inside spawned ranks (see tests/_mp.py).  Each takes (rank, world, *args)."""
+import copy
+import math
+
+import torch
+import torch.distributed as dist
+
+
+def _dev(rank):
+    return torch.device("cuda", rank) if torch.cuda.is_available() and dist.get_backend() == "nccl" else torch.device("cpu")
+
+
+# --------------------------------------------------------------------------- collectives
+def allreduce_demo(rank, world):
+    """pytorch_allreduce.py:21-33: distinct int64 triples per rank, summed everywhere."""
+    from dtds_b200 import comm
+    base = {0: [1, 2, 3], 1: [10, 20, 30], 2: [4, 5, 6]}
+    t = torch.tensor(base.get(rank, [rank, rank, rank]), device=_dev(rank))
+    comm.all_reduce(t)
+    want = [sum(base.get(r, [r, r, r])[i] for r in range(world)) for i in range(3)]
+    assert t.tolist() == want, (t.tolist(), want)
+
+
+def collectives_match_torch(rank, world):
+    """Custom P2P kernels vs torch.distributed on the same inputs, many sizes and dtypes."""
+    from dtds_b200 import comm
+    dev = _dev(rank)
+    ctx = comm.symm_context()
+    torch.manual_seed(100 + rank)
+    for dtype in (torch.bfloat16, torch.float32, torch.int64):
+        for n in (1, 3, 8, 1000, 4096, 65536 + 8, 1 << 20, (1 << 22) + 24):
+            x = torch.randint(-50, 50, (n,), device=dev).to(dtype) if dtype == torch.int64 \
+                else torch.randn(n, device=dev).to(dtype)
+            want = x.clone().float() if dtype != torch.int64 else x.clone()
+            dist.all_reduce(want)
+            got = x.clone()
+            comm.all_reduce(got)
+            if dtype == torch.int64:
+                assert torch.equal(got, want), (dtype, n)
+            else:
+                tol = 2e-2 if dtype == torch.bfloat16 else 1e-5
+                err = (got.float() - want.float()).abs().max().item()
+                assert err <= tol * (want.abs().max().item() + 1), (dtype, n, err)
+    # symmetric-buffer primitives
+    n_per = 4096 + 64
+    buf = ctx.new_buffer(max(n_per * world * 4, (1 << 16) * 2))
+    t = buf.tensor(torch.float32, n_per * world)
+    t.copy_(torch.arange(n_per * world, device=dev, dtype=torch.float32) * (rank + 1))
+    torch.cuda.synchronize(); dist.barrier()
+    out = torch.empty(n_per, device=dev)
+    ctx.reduce_scatter(buf, 0, n_per * 4, torch.float32, out, scale=0.5)
+    tot = sum(r + 1 for r in range(world))
+    want = torch.arange(rank * n_per, (rank + 1) * n_per, device=dev, dtype=torch.float32) * tot * 0.5
+    assert torch.allclose(out, want), "reduce_scatter"
+    src = torch.full((n_per,), float(rank + 1), device=dev)
+    ctx.all_gather(buf, 0, n_per * 4, src)
+    torch.cuda.synchronize()
+    for r in range(world):
+        assert torch.all(t[r * n_per:(r + 1) * n_per] == r + 1), "all_gather"
+    t.fill_(float(rank + 7))
+    torch.cuda.synchronize(); dist.barrier()
+    ctx.broadcast(buf, 0, n_per * world * 4, root=world - 1)
+    torch.cuda.synchronize()
+    assert torch.all(t == world - 1 + 7), "broadcast"
+    # stress: many back-to-back in-place all-reduces reuse the signal pads without host syncs
+    g = buf.tensor(torch.bfloat16, 1 << 16)
+    for it in range(200):
+        g.fill_(1.0)
+        ctx.all_reduce(buf, 0, (1 << 16) * 2, torch.bfloat16, scale=1.0 / world)
+    torch.cuda.synchronize()
+    assert torch.all(g == 1.0), "repeated all_reduce"
+
+
+def zero_step_matches_reference(rank, world):
+    """Fused reduce-scatter + Adam + all-gather kernel vs all-reduce + full Adam."""
+    from dtds_b200 import comm
+    from dtds_b200.ops import reference as ref
+    dev = _dev(rank)
+    ctx = comm.symm_context()
+    per = 8 * 1024
+    n = per * world
+    gbuf, pbuf = ctx.new_buffer(n * 2), ctx.new_buffer(n * 2)
+    g, p = gbuf.tensor(torch.bfloat16, n), pbuf.tensor(torch.bfloat16, n)
+    torch.manual_seed(7)
+    p0 = torch.randn(n, device=dev)
+    p.copy_(p0)
+    master = p.float()[rank * per:(rank + 1) * per].clone()
+    m, v = torch.zeros(per, device=dev), torch.zeros(per, device=dev)
+    step = torch.zeros((), dtype=torch.int32, device=dev)
+    ref_p, ref_m, ref_v = p.float().clone(), torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    for it in range(3):
+        torch.manual_seed(1000 + 10 * it + rank)
+        g.copy_(torch.randn(n, device=dev))
+        gsum = g.float().clone()
+        dist.all_reduce(gsum)
+        gavg = gsum / world
+        torch.cuda.synchronize(); dist.barrier()
+        ctx.zero_step(gbuf, pbuf, goff_elems=0, poff_elems=0, per_rank_elems=per, master=master, m=m, v=v,
+                      step=step, lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0,
+                      grad_scale=1.0 / world)
+        step += 1
+        ref.adam_step(ref_p, gavg, ref_m, ref_v, it + 1, lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8,
+                      weight_decay=0.0)
+        torch.cuda.synchronize(); dist.barrier()
+        err = (p.float() - ref_p).abs().max().item()
+        assert err < 2e-2, f"iter {it}: params differ by {err}"
+        own = (master - ref_p[rank * per:(rank + 1) * per]).abs().max().item()
+        assert own < 2e-3, f"iter {it}: master partition differs by {own}"
+
+
+# --------------------------------------------------------------------------- DDP
+def _tiny_bert(dev, dtype, seed=0, dropout=0.0):
+    from dtds_b200.models import build_model, get_config
+    torch.manual_seed(seed)
+    cfg = get_config("bert-tiny").replace(hidden_dropout_prob=dropout, attention_probs_dropout_prob=dropout)
+    return cfg, build_model(cfg).to(device=dev, dtype=dtype)
+
+
+def ddp_matches_single_process(rank, world, bucket_mb=0.05):
+    """Averaged DDP gradients == gradients of the same model on the concatenated batch."""
+    from dtds_b200.parallel.ddp import DistributedDataParallel
+    dev = _dev(rank)
+    dtype = torch.bfloat16 if dev.type == "cuda" else torch.float32
+    cfg, model = _tiny_bert(dev, dtype, seed=rank)  # different init per rank: ctor must broadcast
+    ddp = DistributedDataParallel(model, bucket_cap_mb=bucket_mb)
+    assert len(ddp.buckets) > 2
+    _, ref_model = _tiny_bert(dev, dtype, seed=0)
+    for a, b in zip(model.parameters(), ref_model.parameters()):
+        assert torch.equal(a.detach().cpu(), b.detach().cpu()), "constructor did not broadcast rank 0"
+    B, S = 2, 128
+    g = torch.Generator().manual_seed(5)
+    ids_all = torch.randint(0, cfg.vocab_size, (world * B, S), generator=g)
+    labels_all = ids_all.clone()
+    labels_all[:, ::2] = -100
+    ids, labels = ids_all[rank * B:(rank + 1) * B].to(dev), labels_all[rank * B:(rank + 1) * B].to(dev)
+    loss = ddp(ids, labels=labels).loss
+    loss.backward()
+    if dev.type == "cuda":
+        torch.cuda.synchronize()
+    ref_loss = ref_model(ids_all.to(dev), labels=labels_all.to(dev)).loss
+    ref_loss.backward()
+    for (n, p), q in zip(model.named_parameters(), ref_model.parameters()):
+        got, want = p.main_grad.float(), q.grad.float()
+        denom = want.abs().max().item() + 1e-6
+        err = (got - want).abs().max().item() / denom
+        tol = 0.06 if dtype == torch.bfloat16 else 1e-4
+        assert err < tol, f"{n}: {err}"
+    # second iteration reuses buckets and signal pads
+    ddp(ids, labels=labels).loss.backward()
+    # no_sync accumulates locally without communication
+    with ddp.no_sync():
+        ddp(ids, labels=labels).loss.backward()
+
+
+def ddp_training_loop(rank, world, use_graph=False):
+    """A few optimizer steps under DDP; all ranks must hold identical parameters afterwards."""
+    from dtds_b200.optim import FusedAdam
+    from dtds_b200.parallel.ddp import DistributedDataParallel
+    dev = _dev(rank)
+    dtype = torch.bfloat16 if dev.type == "cuda" else torch.float32
+    cfg, model = _tiny_bert(dev, dtype, seed=0, dropout=0.1)
+    ddp = DistributedDataParallel(model, bucket_cap_mb=0.1)
+    opt = FusedAdam(model.parameters(), lr=1e-3)
+    g = torch.Generator().manual_seed(50 + rank)
+    ids = torch.randint(0, cfg.vocab_size, (2, 128), generator=g).to(dev)
+    labels = ids.clone()
+
+    def step(i, l):
+        opt.zero_grad()
+        loss = ddp(i, labels=l).loss
+        loss.backward()
+        opt.step()
+        return loss
+
+    if use_graph:
+        from dtds_b200.parallel.graph import GraphedStep
+        gs = GraphedStep(step, [ids, labels], warmup=2)
+        losses = [gs(ids, labels).item() for _ in range(6)]
+    else:
+        losses = [step(ids, labels).item() for _ in range(6)]
+    assert losses[-1] < losses[0], losses
+    flat = ddp.flat.param_flat.float()
+    other = flat.clone()
+    dist.broadcast(other, src=0)
+    assert torch.equal(flat, other), "replicas diverged"
+
+
+# --------------------------------------------------------------------------- ZeRO
+def _ds_config(stage, bf16):
+    return {"train_micro_batch_size_per_gpu": 2,
+            "optimizer": {"type": "Adam", "params": {"lr": 1e-3}},
+            "comms_logger": {"enabled": True, "verbose": False, "prof_all": True, "debug": False},
+            "zero_optimization": {"stage": stage, "reduce_bucket_size": 2e5},
+            "bf16": {"enabled": bf16}}
+
+
+def zero_stages_match_stage0(rank, world, arch="bloom-tiny"):
+    """Parameters after k steps are the same for ZeRO-0/1/2/3 (same data, same init)."""
+    from dtds_b200 import comm
+    from dtds_b200.models import build_model, get_config
+    from dtds_b200.parallel import zero
+    dev = _dev(rank)
+    bf16 = dev.type == "cuda"
+    cfg = get_config(arch).replace(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    g = torch.Generator().manual_seed(11 + rank)
+    ids = torch.randint(0, cfg.vocab_size, (2, 128), generator=g)
+    results, mem = {}, {}
+    for stage in (0, 1, 2, 3):
+        torch.manual_seed(0)
+        model = build_model(cfg)
+        engine, opt, _, _ = zero.initialize(model=model, model_parameters=model.parameters(),
+                                            config=_ds_config(stage, bf16))
+        assert engine.zero_optimization_stage() == stage
+        pg = opt.param_groups[0]
+        assert pg["lr"] == 1e-3 and tuple(pg["betas"]) == (0.9, 0.999) and pg["eps"] == 1e-8
+        engine.train()
+        losses = []
+        for _ in range(4):
+            loss = engine(ids.to(dev), labels=ids.to(dev)).loss
+            engine.backward(loss)
+            engine.step()
+            losses.append(loss.item())
+        assert losses[-1] < losses[0], (stage, losses)
+        sd = engine.consolidated_fp32_state_dict()
+        results[stage] = torch.cat([v.flatten().float().cpu() for k, v in sorted(sd.items())])
+        mem[stage] = engine.optimizer_state_bytes()
+        if stage == 3:
+            assert engine.param3.resident_parameter_bytes() * world <= \
+                sum(p._numel for p in engine.flat.params) * (2 if bf16 else 4) * 1.2 + 65536 * world
+    for stage in (1, 2, 3):
+        err = (results[stage] - results[0]).abs().max().item()
+        tol = 2e-2 if bf16 else 1e-5
+        assert err < tol, f"stage {stage} differs from stage 0 by {err}"
+        assert mem[stage] * world <= mem[0] * 1.05 + 4096 * world, (stage, mem)
+    total = comm.comms_logger.total_latency_ms()
+    assert total > 0 and comm.comms_logger.comms_dict, "comms logger recorded nothing"
+
+
+# --------------------------------------------------------------------------- pipeline
+def pipeline_matches_single_process(rank, world, chunks=4):
+    """GPipe over `world` stages: gradients and loss equal the single-process full-batch run."""
+    from dtds_b200.models import get_config
+    from dtds_b200.models.bert_mp import BertModelWithMP
+    from dtds_b200.ops import functional as Fn
+    dev = _dev(rank)
+    dtype = torch.bfloat16 if dev.type == "cuda" else torch.float32
+    cfg = get_config("bert-tiny").replace(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0,
+                                          num_hidden_layers=4)
+    torch.manual_seed(0)
+    bert = BertModelWithMP(cfg, dtype=dtype)
+    assert bert.device_count == world and bert.distributed
+    # a full single-process copy with identical weights, built without touching the process group
+    torch.manual_seed(0)
+    from dtds_b200.models.bert import BertEmbeddings, BertLayer, BertOnlyMLMHead
+    cfg_u = cfg.replace(tie_word_embeddings=False)
+    # every stage draws the same random stream: rebuild ALL modules in order, keep mine in sync
+    torch.manual_seed(123)
+    full = [BertEmbeddings(cfg_u)] + [BertLayer(cfg_u) for _ in range(cfg.num_hidden_layers)] + [BertOnlyMLMHead(cfg_u)]
+    full = [m.to(device=dev, dtype=dtype) for m in full]
+    for idx in bert._mine:
+        bert._module(idx).load_state_dict(full[idx].state_dict())
+    B, S = 8, 128
+    g = torch.Generator().manual_seed(3)
+    ids = torch.randint(0, cfg.vocab_size, (B, S), generator=g)
+    labels = ids.clone()
+    labels[:, ::3] = -100
+    pipe = bert.to_pipeline(chunks)
+    loss = pipe.forward_backward(ids, labels)
+    # reference: all modules in this process, whole batch
+    h = full[0](ids.to(dev))
+    for m in full[1:-1]:
+        h = m(h)
+    ref_loss = full[-1](h, labels=labels.to(dev))
+    ref_loss.backward()
+    if rank == world - 1:
+        assert abs(loss.item() - ref_loss.item()) < (3e-2 if dtype == torch.bfloat16 else 1e-4), (loss.item(), ref_loss.item())
+    tol = 0.08 if dtype == torch.bfloat16 else 1e-3
+    for idx in bert._mine:
+        for (n, p), q in zip(bert._module(idx).named_parameters(), full[idx].parameters()):
+            denom = q.grad.float().abs().max().item() + 1e-6
+            err = (p.grad.float() - q.grad.float()).abs().max().item() / denom
+            assert err < tol, f"module {idx} {n}: {err}"
+    idle = bert.collect_idle_time()
+    assert set(idle.keys()) == set(range(world))

@@ -1,0 +1,23 @@
+"""CPU / gloo world_size=2 plumbing tests (BASELINE.json config 1): process-group bootstrap,
+logged collectives, DDP bucket schedule and gradient equivalence, training loop."""
+from _mp import run_distributed
+
+
+def test_allreduce_demo_gloo_world3():
+    run_distributed("allreduce_demo", world=3, backend="gloo")
+
+
+def test_ddp_matches_single_process_gloo():
+    run_distributed("ddp_matches_single_process", world=2, backend="gloo")
+
+
+def test_ddp_training_loop_gloo():
+    run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False,))
+
+
+def test_zero_stages_match_stage0_gloo():
+    run_distributed("zero_stages_match_stage0", world=2, backend="gloo", timeout=600)
+
+
+def test_gpipe_matches_single_process_gloo():
+    run_distributed("pipeline_matches_single_process", world=2, backend="gloo", args=(4,), timeout=600)

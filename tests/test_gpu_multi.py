@@ -1,0 +1,40 @@
+"""Multi-GPU tests (need >= 2 visible GPUs): custom P2P collectives vs NCCL, the fused ZeRO step
+kernel, and DDP equivalence / training with and without CUDA graphs."""
+import pytest
+import torch
+
+from _mp import run_distributed
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")]
+
+
+def test_allreduce_demo():
+    run_distributed("allreduce_demo", world=2, backend="nccl")
+
+
+def test_collectives_match_torch():
+    run_distributed("collectives_match_torch", world=2, backend="nccl")
+
+
+def test_zero_step_kernel():
+    run_distributed("zero_step_matches_reference", world=2, backend="nccl")
+
+
+def test_ddp_matches_single_process():
+    run_distributed("ddp_matches_single_process", world=2, backend="nccl")
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_ddp_training_loop(use_graph):
+    run_distributed("ddp_training_loop", world=2, backend="nccl", args=(use_graph,))
+
+
+@pytest.mark.parametrize("arch", ["bloom-tiny", "bert-tiny"])
+def test_zero_stages_match_stage0(arch):
+    run_distributed("zero_stages_match_stage0", world=2, backend="nccl", args=(arch,), timeout=600)
+
+
+@pytest.mark.parametrize("chunks", [1, 4])
+def test_pipeline_matches_single_process(chunks):
+    run_distributed("pipeline_matches_single_process", world=2, backend="nccl", args=(chunks,), timeout=600)

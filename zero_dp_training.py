@@ -1,0 +1,121 @@
+"""ZeRO data-parallel causal-LM training (stages 0-3) behind the DeepSpeed-shaped engine.
+
+Command line of the reference (``--model-name``, ``--batch-size`` per GPU, ``--training-steps``,
+``--stage``; unknown arguments such as the launcher's ``--local_rank`` are swallowed) and the same
+console output: the stage line, the optimizer line, a MEMSTATS line per step on rank 0, the total
+training time, the per-collective summary table and the total communication latency.
+
+Launch one process per GPU with the in-repo launcher (or torchrun):
+
+    python -m dtds_b200.launch --nproc-per-node 8 zero_dp_training.py --stage 3
+    python zero_dp_training.py --stage 0                         # single process
+
+``--model-name`` takes the in-repo configurations (bigscience/bloom-560m, facebook/opt-125m,
+bloom-tiny, ...) or ``scale:<hidden>x<layers>`` for a hand-sized multi-billion-parameter decoder.
+Weights are random-init and the rows synthetic (no hub access).  Unlike the reference the
+launcher's ``--model_name`` spelling is accepted too (its scripts/launch-multinode.sh passes the
+underscore form, which argparse silently dropped: quirk Q3), and latencies are labelled in the
+unit they are measured in (milliseconds; quirk Q2).
+"""
+import argparse
+import os
+import time
+
+import torch
+from torch.utils.data import DataLoader
+from torch.utils.data.distributed import DistributedSampler
+from tqdm import tqdm
+
+from util import load_wikitext, synthetic_collator, synthetic_tokenizer
+
+
+def resolve_config(model_name):
+    from dtds_b200.models import get_config, transformer_scale_config
+    if model_name.startswith("scale:"):
+        hidden, layers = model_name.split(":", 1)[1].lower().split("x")
+        return transformer_scale_config(int(hidden), int(layers))
+    return get_config(model_name)
+
+
+def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_len=512, quiet=False):
+    from dtds_b200 import comm
+    from dtds_b200.models import build_model
+    from dtds_b200.parallel import zero
+    from dtds_b200.utils import memory_status
+
+    rank = int(os.getenv("LOCAL_RANK", "0"))
+    world_size = int(os.getenv("WORLD_SIZE", "1"))
+    on_gpu = torch.cuda.is_available()
+    device = torch.device("cuda", rank) if on_gpu else torch.device("cpu")
+    if world_size > 1:
+        comm.init_process_group()
+
+    cfg = resolve_config(model_name)
+    torch.manual_seed(0)
+    model = build_model(cfg)
+
+    ds_config = {
+        "train_micro_batch_size_per_gpu": batch_size,
+        "optimizer": {"type": "Adam", "params": {"lr": 0.00015}},
+        "comms_logger": {"enabled": True, "verbose": False, "prof_all": True, "debug": False},
+        "zero_optimization": {"stage": stage, "reduce_bucket_size": 5e6},
+        "bf16": {"enabled": on_gpu if bf16 is None else bf16},
+    }
+    model_engine, optimizer, _, _ = zero.initialize(model=model, model_parameters=model.parameters(),
+                                                    config=ds_config)
+    print(f"Device {rank} - ZeRO Stage: {model_engine.zero_optimization_stage()}")
+    group = optimizer.param_groups[0]
+    print(f"Device {rank} - Optimizer: lr={group['lr']}; betas={group['betas']}; eps={group['eps']}; "
+          f"parameter count={sum(p._numel for p in group['params']):,}")
+
+    tokenizer = synthetic_tokenizer(cfg)
+    collator = synthetic_collator(tokenizer, mlm=False)
+    seq = min(seq_len, cfg.max_position_embeddings)
+    train_dataset = load_wikitext(tokenizer, collator, max_length=seq).select(range(batch_size * training_steps))
+    train_dataloader = DataLoader(train_dataset, batch_size=batch_size, shuffle=False,
+                                  sampler=DistributedSampler(train_dataset, num_replicas=world_size,
+                                                             rank=comm.get_rank()))
+    model_engine.train()
+    comm.comms_logger.resolve()
+    comm.comms_logger.comms_dict = {}     # only the training loop counts towards the totals below
+
+    training_start_time = time.time()
+    progress_bar = tqdm(range(training_steps)) if rank == 0 and not quiet else None
+    for batch in train_dataloader:
+        input_ids = batch["input_ids"].to(device)
+        labels = batch["labels"].to(device)
+        loss = model_engine(input_ids, labels=labels).loss
+        model_engine.backward(loss)
+        model_engine.step()
+        if rank == 0:
+            if not quiet:
+                memory_status("Memory stats after training step:")
+            if progress_bar is not None:
+                progress_bar.update(1)
+    if on_gpu:
+        torch.cuda.synchronize()
+    training_end_time = time.time()
+    if rank == 0:
+        print(f"\nTotal Training Time: {training_end_time - training_start_time:.2f} seconds")
+
+    total_comms_latency = comm.comms_logger.total_latency_ms()
+    comm.log_summary()
+    if rank == 0:
+        print(f"\nTotal Communication Latency: {total_comms_latency:.2f} ms "
+              f"({total_comms_latency / 1e3:.3f} seconds)")
+    comm.destroy_process_group()
+    return model_engine
+
+
+if __name__ == "__main__":
+    parser = argparse.ArgumentParser()
+    parser.add_argument("--model-name", "--model_name", dest="model_name", type=str, default="bigscience/bloom-560m")
+    parser.add_argument("--batch-size", type=int, default=1)
+    parser.add_argument("--training-steps", type=int, default=100)
+    parser.add_argument("--stage", type=int, default=0)
+    parser.add_argument("--seq-len", type=int, default=512)
+    parser.add_argument("--fp32", action="store_true", help="keep fp32 parameters (library collectives)")
+    parser.add_argument("--quiet", action="store_true", help="no per-step MEMSTATS / progress bar")
+    args, extra_args = parser.parse_known_args()
+    train(args.model_name, args.batch_size, args.training_steps, args.stage, *extra_args,
+          bf16=False if args.fp32 else None, seq_len=args.seq_len, quiet=args.quiet)
