@@ -32,7 +32,7 @@ namespace dtds {
 
 constexpr int kMaxRanks = 16;
 constexpr int kCommThreads = 512;
-constexpr int kMaxCommBlocks = 64;  // signal pad holds kMaxCommBlocks * kMaxRanks flags per use
+constexpr int kMaxCommBlocks = 128;  // signal pad holds kMaxCommBlocks * kMaxRanks flags per use
 
 struct PeerTable {
   void* data[kMaxRanks];
@@ -151,6 +151,32 @@ __device__ __forceinline__ void reduce_vec(const PeerTable& pt, size_t off,
       if (base + k < pt.world) Vec<T>::add(raw[k], acc);
   }
 }
+// Two vectors at once: all 2 x world peer loads are in flight before the first add.  With 128
+// blocks x 512 threads this keeps several MB outstanding, enough to cover NVLink latency
+// (~2 us) at full link bandwidth.
+template <typename T>
+__device__ __forceinline__ void reduce_vec2(const PeerTable& pt, size_t off0, size_t off1,
+                                            typename Vec<T>::Acc (&a0)[Vec<T>::N],
+                                            typename Vec<T>::Acc (&a1)[Vec<T>::N]) {
+#pragma unroll
+  for (int i = 0; i < Vec<T>::N; ++i) { a0[i] = 0; a1[i] = 0; }
+  for (int base = 0; base < pt.world; base += 8) {
+    uint4 r0[8], r1[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (base + k < pt.world) {
+        int peer = pt.rank + base + k;
+        if (peer >= pt.world) peer -= pt.world;
+        const char* b = static_cast<const char*>(pt.data[peer]);
+        r0[k] = ld_peer_v4(b + off0);
+        r1[k] = ld_peer_v4(b + off1);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (base + k < pt.world) { Vec<T>::add(r0[k], a0); Vec<T>::add(r1[k], a1); }
+  }
+}
 template <typename T>
 __device__ __forceinline__ void scale_vec(typename Vec<T>::Acc (&acc)[Vec<T>::N], float scale) {
   if (scale != 1.f) {
@@ -180,17 +206,18 @@ allreduce_oneshot_kernel(PeerTable pt, void* out, size_t off_bytes, size_t nvec,
 // Two-shot, in place on the symmetric buffer: rank r reduces slice r (pulling from all peers) and
 // pushes the reduced slice into every peer's buffer.  Per rank: (n-1)/n of the message in over
 // NVLink and (n-1)/n out.  `scale` (e.g. 1/world for gradient averaging) is applied once.
-template <typename T>
-__global__ void __launch_bounds__(kCommThreads)
+// ILP = 2: standalone / bandwidth-critical (128 registers, one block per SM).  ILP = 1: capped at
+// 64 registers so a block fits on an SM next to a resident persistent GEMM CTA — the variant the
+// DDP engine uses for buckets reduced while backward is still running.
+template <typename T, int ILP>
+__global__ void __launch_bounds__(kCommThreads, ILP == 1 ? 2 : 1)
 allreduce_twoshot_kernel(PeerTable pt, size_t off_bytes, size_t nvec, float scale) {
   cross_gpu_barrier(pt, 0);
   const size_t per = (nvec + pt.world - 1) / pt.world;
   const size_t v0 = per * pt.rank;
   const size_t v1 = min(nvec, v0 + per);
-  for (size_t v = v0 + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < v1;
-       v += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    typename Vec<T>::Acc acc[Vec<T>::N];
-    reduce_vec<T>(pt, off_bytes + v * 16, acc);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  auto push = [&](size_t v, typename Vec<T>::Acc (&acc)[Vec<T>::N]) {
     scale_vec<T>(acc, scale);
     const uint4 packed = Vec<T>::pack(acc);
 #pragma unroll 1
@@ -198,6 +225,26 @@ allreduce_twoshot_kernel(PeerTable pt, size_t off_bytes, size_t nvec, float scal
       const int peer = (pt.rank + k) % pt.world;
       *reinterpret_cast<uint4*>(static_cast<char*>(pt.data[peer]) + off_bytes + v * 16) = packed;
     }
+  };
+  size_t v = v0 + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if constexpr (ILP == 2) {
+    for (; v + stride < v1; v += 2 * stride) {
+      typename Vec<T>::Acc a0[Vec<T>::N], a1[Vec<T>::N];
+      reduce_vec2<T>(pt, off_bytes + v * 16, off_bytes + (v + stride) * 16, a0, a1);
+      push(v, a0);
+      push(v + stride, a1);
+    }
+  } else {
+    for (; v + stride < v1; v += stride) {
+      typename Vec<T>::Acc acc[Vec<T>::N];
+      reduce_vec<T>(pt, off_bytes + v * 16, acc);
+      push(v, acc);
+    }
+  }
+  if (v < v1) {
+    typename Vec<T>::Acc acc[Vec<T>::N];
+    reduce_vec<T>(pt, off_bytes + v * 16, acc);
+    push(v, acc);
   }
   cross_gpu_barrier(pt, 1);
 }
@@ -334,7 +381,7 @@ static std::mutex g_mu;
 static std::vector<SymmAlloc> g_allocs;
 
 static int comm_blocks(size_t nvec, int requested) {
-  int b = requested > 0 ? requested : 48;
+  int b = requested > 0 ? requested : 96;
   if (b > kMaxCommBlocks) b = kMaxCommBlocks;
   const size_t need = (nvec + kCommThreads - 1) / kCommThreads;
   if (need < static_cast<size_t>(b)) b = need > 0 ? static_cast<int>(need) : 1;
@@ -422,9 +469,9 @@ extern "C" int dtds_allreduce(const unsigned long long* data_ptrs,
   const size_t nvec = nbytes / 16;
   // The one-shot kernel writes while peers may still be reading, so it needs a destination
   // outside the symmetric buffer; in-place calls always take the two-shot path.
-  if (out == nullptr) algo = 2;
+  if (out == nullptr && algo != 3) algo = 2;
   if (algo == 0) algo = (nbytes <= (512u << 10)) ? 1 : 2;
-  const int nb = comm_blocks(algo == 1 ? nvec : (nvec + world - 1) / world, blocks);
+  const int nb = comm_blocks(algo == 1 ? nvec : (nvec + world - 1) / world, blocks > 0 ? blocks : (algo == 3 ? 32 : 0));
   if (algo == 1) {
     void* dst = out;
     if (dtype == 0) allreduce_oneshot_kernel<__nv_bfloat16><<<nb, kCommThreads, 0, stream>>>(pt, dst, off_bytes, nvec, scale);
@@ -435,9 +482,16 @@ extern "C" int dtds_allreduce(const unsigned long long* data_ptrs,
       fprintf(stderr, "[dtds] allreduce: the two-shot algorithm works in place\n");
       return -3;
     }
-    if (dtype == 0) allreduce_twoshot_kernel<__nv_bfloat16><<<nb, kCommThreads, 0, stream>>>(pt, off_bytes, nvec, scale);
-    else if (dtype == 1) allreduce_twoshot_kernel<float><<<nb, kCommThreads, 0, stream>>>(pt, off_bytes, nvec, scale);
-    else allreduce_twoshot_kernel<long long><<<nb, kCommThreads, 0, stream>>>(pt, off_bytes, nvec, scale);
+    const bool overlap = algo == 3;  // co-resident with compute: low-register variant
+    if (dtype == 0) {
+      if (overlap) allreduce_twoshot_kernel<__nv_bfloat16, 1><<<nb, kCommThreads, 0, stream>>>(pt, off_bytes, nvec, scale);
+      else allreduce_twoshot_kernel<__nv_bfloat16, 2><<<nb, kCommThreads, 0, stream>>>(pt, off_bytes, nvec, scale);
+    } else if (dtype == 1) {
+      if (overlap) allreduce_twoshot_kernel<float, 1><<<nb, kCommThreads, 0, stream>>>(pt, off_bytes, nvec, scale);
+      else allreduce_twoshot_kernel<float, 2><<<nb, kCommThreads, 0, stream>>>(pt, off_bytes, nvec, scale);
+    } else {
+      allreduce_twoshot_kernel<long long, 1><<<nb, kCommThreads, 0, stream>>>(pt, off_bytes, nvec, scale);
+    }
   }
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;

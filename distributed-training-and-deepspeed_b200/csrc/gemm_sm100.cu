@@ -61,7 +61,9 @@ struct GemmParams {
 };
 
 template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+// 96 registers: 320 threads x 96 leaves room on the SM for a 512-thread, 64-register
+// communication block (overlapped gradient-bucket all-reduce) next to this persistent CTA.
+__global__ void __maxnreg__(96)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmParams p) {
   using Cfg = GemmCfg<BN>;

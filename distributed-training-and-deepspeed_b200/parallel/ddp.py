@@ -176,7 +176,7 @@ class DistributedDataParallel(nn.Module):
                 e = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
                 s.record()
                 ctx.all_reduce(self.flat.grad_buf, b.lo * esz, nbytes, g.dtype, scale=1.0 / self.world,
-                               algo=2, blocks=self.comm_blocks)
+                               algo=3, blocks=self.comm_blocks)
                 e.record()
             comm.comms_logger.record_events("all_reduce", nbytes, self.world, s, e)
             self._events.append(e)

@@ -205,7 +205,11 @@ class Zero3ParamManager:
 
     def _post_bwd(self, blk):
         def hook(module, grad_input, grad_output):
-            self._release(blk)
+            # If no input of the block requires grad (the embedding block) PyTorch fires this hook
+            # BEFORE the block's backward has run; releasing then would pull the parameters out
+            # from under it.  Such blocks are dropped at the end of the step instead.
+            if any(g is not None for g in grad_input):
+                self._release(blk)
         return hook
 
     def release_all(self) -> None:

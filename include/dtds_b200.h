@@ -116,7 +116,8 @@ int dtds_symm_import(const void* handle, unsigned long long* out_ptr);
 int dtds_symm_close(unsigned long long ptr);
 size_t dtds_signal_pad_bytes(void);
 /* dtype: 0 bf16, 1 fp32, 2 int64 (sum).  algo: 0 auto, 1 one-shot (needs `out` outside the
- * symmetric buffer), 2 two-shot (in place, out = NULL).  `scale` is applied once to the sum.   */
+ * symmetric buffer), 2 two-shot (in place, out = NULL), 3 two-shot low-register variant that can
+ * share an SM with a resident GEMM CTA (overlapped gradient buckets).  `scale` is applied once.  */
 int dtds_allreduce(const unsigned long long* data_ptrs, const unsigned long long* signal_ptrs,
                    int rank, int world, void* out, size_t off_bytes, size_t nbytes, int dtype,
                    float scale, int algo, int blocks, cudaStream_t stream);
