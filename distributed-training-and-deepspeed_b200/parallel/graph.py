@@ -34,7 +34,6 @@ class GraphedStep:
         for s, t in zip(self.static_inputs, example_inputs):
             s.copy_(t)
         self.seed_offset = torch.zeros(1, dtype=torch.int64, device=self.device)
-        K.set_seed_offset_tensor(self.seed_offset)
         self.graph = None
         self.static_loss = None
         self._stream = torch.cuda.Stream(self.device)
@@ -51,7 +50,13 @@ class GraphedStep:
         torch.cuda.synchronize(self.device)
 
     def _one(self):
-        loss = self.step_fn(*self.static_inputs)
+        # The device-side seed offset is only registered while this step is being recorded (its
+        # address gets baked into the captured kernels); eager code elsewhere is unaffected.
+        K.set_seed_offset_tensor(self.seed_offset)
+        try:
+            loss = self.step_fn(*self.static_inputs)
+        finally:
+            K.set_seed_offset_tensor(None)
         self.seed_offset.add_(1)
         return loss
 
