@@ -683,3 +683,74 @@ extern "C" int dtds_mse(const void* x, const void* t, void* dx, float* loss /* z
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// Column sum without any allocation by caller or callee.
+//
+// dtds_colsum() needs a small zero-initialised fp32 scratch (per-column partial sums plus one
+// arrival counter per 64-column tile) that its caller has to allocate.  Some hosts of this
+// library cannot allocate device memory at the point where they need a bias gradient: code
+// running while a CUDA graph is being captured (cudaMalloc is illegal during capture), code
+// inside a framework whose caching allocator owns all device memory and must not be re-entered
+// (an allocator callback, a destructor, an out-of-memory handler), and plain C callers that only
+// hold the tensors they were handed.  For them the scratch lives in this library's image: a
+// file-scope __device__ array of fixed size that every GPU which loads the library keeps until
+// the process exits (kNoAllocMaxCols + kNoAllocMaxTiles 4-byte words = 132 KiB per GPU).
+//
+// In host code `g_colsum_scratch` is only a handle for the symbol, not a device address, so the
+// entry point asks the runtime for the address (cudaGetSymbolAddress) once per device, with that
+// device current, and hands the returned pointer to the kernel.
+constexpr int kNoAllocMaxCols = 32768;
+constexpr int kNoAllocMaxTiles = kNoAllocMaxCols / 64;
+static __device__ __align__(256) float g_colsum_scratch[kNoAllocMaxCols + kNoAllocMaxTiles];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_scratch_addr[kMaxDevices] = {nullptr};
+}  // namespace
+
+extern "C" int dtds_colsum_noalloc(const void* x, int rows, int cols, int ld, void* out,
+                                   int out_fp32, int accumulate, cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) return 0;
+  if (cols > kNoAllocMaxCols) {
+    fprintf(stderr,
+            "[dtds] colsum_noalloc: cols = %d exceeds the built-in scratch (max %d columns); use "
+            "dtds_colsum with a caller-provided scratch instead\n",
+            cols, kNoAllocMaxCols);
+    return -2;
+  }
+  int dev = 0;
+  DTDS_HOST_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) {
+    fprintf(stderr, "[dtds] colsum_noalloc: device ordinal %d out of range\n", dev);
+    return -3;
+  }
+  if (g_scratch_addr[dev] == nullptr) {
+    // One-time set-up for this device (it is the current one): resolve the symbol to its address
+    // on THIS device and start from a clean scratch.  Not an allocation, but it is not something
+    // to record into a CUDA graph either: make the first call on each device before any capture.
+    float* addr = nullptr;
+    DTDS_HOST_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&addr), g_colsum_scratch));
+    DTDS_HOST_CHECK(cudaMemsetAsync(addr, 0, sizeof(float) * (kNoAllocMaxCols + kNoAllocMaxTiles), stream));
+    g_scratch_addr[dev] = addr;
+  }
+  float* scratch = g_scratch_addr[dev];
+  const int tiles = (cols + 63) / 64;
+  int splits = 1;
+  if (tiles < 2 * dtds::sm_count()) {
+    splits = (2 * dtds::sm_count() + tiles - 1) / tiles;
+    const int max_splits = (rows + 63) / 64;
+    if (splits > max_splits) splits = max_splits;
+    if (splits > 64) splits = 64;
+    if (splits < 1) splits = 1;
+  }
+  // Partial sums occupy [0, tiles*64); the per-tile arrival counters sit at a fixed offset behind
+  // the largest possible sum region so calls with different `cols` never alias the two.  The
+  // kernel re-zeroes everything it touched before it exits, so consecutive calls need no memset.
+  unsigned int* counters = reinterpret_cast<unsigned int*>(scratch + kNoAllocMaxCols);
+  dim3 grid(tiles, splits);
+  dtds::colsum_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), rows, cols, ld,
+                                                scratch, counters, out, out_fp32, accumulate);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -145,6 +145,19 @@ int dtds_zero_step(const unsigned long long* grad_ptrs, const unsigned long long
 int dtds_copy_segments(const unsigned long long* src_ptrs, const unsigned long long* dst_ptrs,
                        const unsigned long long* nbytes, int nseg, int blocks, cudaStream_t stream);
 
+/* ---- Column sum that allocates nothing (no counterpart in the reference: it has no native code
+ *      and no allocation-free entry points) ----------------------------------------------------
+ * Same result as dtds_colsum, for callers that cannot allocate device memory where they need it:
+ * code running under CUDA-graph capture, code inside a caching allocator's callbacks or
+ * out-of-memory path, and C hosts that own no allocator.  The fp32 scratch is a fixed
+ * __device__ array inside the library (132 KiB on every GPU that loads it, until process exit).
+ * Limits and rules: cols <= 32768 (larger -> error code -2 and a message, nothing is launched);
+ * the first call on each device resolves the array's address and clears it, so make that call
+ * outside any stream capture; every call uses the same array, so two calls whose kernels could
+ * overlap on the GPU (different streams without ordering) race — serialise them.                */
+int dtds_colsum_noalloc(const void* x, int rows, int cols, int ld, void* out, int out_fp32,
+                        int accumulate, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
