@@ -1,0 +1,97 @@
+"""CPU checks of the model families: parameter counts of SURVEY.md §2.6, state-dict names,
+equivalence with HF BERT, TransformerBlock parity with an HF OPT layer, config surface."""
+import pytest
+import torch
+
+from dtds_b200.models import (BertForMaskedLM, TransformerBlock, build_model, count_parameters,
+                              from_hf_state_dict, get_config, to_hf_state_dict)
+from dtds_b200.models.bert_mp import BertModelWithMP
+from dtds_b200.parallel.pipeline import split_sizes
+
+
+@pytest.mark.parametrize("name,count", [("bert-base-cased", 108_340_804), ("bert-large-cased", 333_610_308),
+                                        ("bigscience/bloom-560m", 559_214_592), ("facebook/opt-125m", 125_239_296)])
+def test_parameter_counts(name, count):
+    with torch.device("meta"):
+        model = build_model(get_config(name))
+    assert count_parameters(model) == count
+
+
+def test_bert_mp_untied_parameter_count_and_prefixes():
+    cfg = get_config("bert-base-cased")
+    with torch.device("meta"):
+        from dtds_b200.models.bert import BertEmbeddings, BertLayer, BertOnlyMLMHead
+        u = cfg.replace(tie_word_embeddings=False)
+        n = sum(p.numel() for p in BertEmbeddings(u).parameters())
+        n += 12 * sum(p.numel() for p in BertLayer(u).parameters())
+        n += sum(p.numel() for p in BertOnlyMLMHead(u).parameters())
+    assert n == 130_609_732
+    tiny = BertModelWithMP(get_config("bert-tiny"), device_count=1)
+    keys = list(tiny.state_dict().keys())
+    assert all(k.split(".")[0] in ("embeddings", "encoders", "head") for k in keys)
+    assert any(k.startswith("encoders.1.") for k in keys)
+
+
+def test_array_split_group_sizes():
+    assert split_sizes(14, 2) == [7, 7]
+    assert split_sizes(14, 3) == [5, 5, 4]
+    assert split_sizes(14, 4) == [4, 4, 3, 3]
+    assert split_sizes(14, 8) == [2, 2, 2, 2, 2, 2, 1, 1]
+
+
+def test_bert_matches_hf_implementation():
+    """Same weights (via the HF-name bridge) -> same logits and same loss as transformers' BERT."""
+    transformers = pytest.importorskip("transformers")
+    cfg = get_config("bert-tiny").replace(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    hf_cfg = transformers.BertConfig(vocab_size=cfg.vocab_size, hidden_size=cfg.hidden_size,
+                                     num_hidden_layers=cfg.num_hidden_layers,
+                                     num_attention_heads=cfg.num_attention_heads,
+                                     intermediate_size=cfg.intermediate_size,
+                                     max_position_embeddings=cfg.max_position_embeddings,
+                                     hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    torch.manual_seed(0)
+    hf = transformers.BertForMaskedLM(hf_cfg).eval()
+    mine = BertForMaskedLM(cfg).eval()
+    from_hf_state_dict(mine, hf.state_dict())
+    ids = torch.randint(0, cfg.vocab_size, (2, 64))
+    labels = ids.clone()
+    labels[:, ::2] = -100
+    with torch.no_grad():
+        ref = hf(input_ids=ids, labels=labels)
+        got = mine(ids, labels=labels, return_logits=True)
+    assert torch.allclose(got.logits, ref.logits, atol=2e-4, rtol=1e-4)
+    assert abs(got.loss.item() - ref.loss.item()) < 1e-4
+    # and back: exported names load into the HF model
+    exported = to_hf_state_dict(mine)
+    missing, unexpected = hf.load_state_dict(exported, strict=False)
+    assert not [k for k in unexpected], unexpected
+
+
+def test_transformer_block_names_and_param_count():
+    from types import SimpleNamespace
+    cfg = SimpleNamespace(hidden_size=128, num_attention_heads=2, ffn_dim=512, enable_bias=True, dropout=0.1,
+                          max_position_embeddings=64)
+    blk = TransformerBlock(cfg)
+    names = {n.split(".")[0] for n, _ in blk.named_parameters()}
+    assert names == {"pre_attention_layer_norm", "k_proj", "v_proj", "q_proj", "out_proj",
+                     "final_layer_norm", "ffn_1", "ffn_2"}
+    mods = {n for n, _ in blk.named_children()}
+    assert {"compute_attention_weights", "attention_weights_softmax", "attention_weights_dropout",
+            "compute_attentions", "attention_output_dropout", "activation", "final_dropout"} <= mods
+    h = 128
+    assert sum(p.numel() for p in blk.parameters()) == 12 * h * h + 13 * h
+    # h = 9216 closed form of the estimator (1,019,335,680)
+    assert 12 * 9216 * 9216 + 13 * 9216 == 1_019_335_680
+    x = torch.randn(2, 16, h)
+    blk.eval()
+    assert blk(x).shape == x.shape
+
+
+def test_causal_lm_shift_and_tied_head():
+    cfg = get_config("opt-tiny").replace(hidden_dropout_prob=0.0)
+    m = build_model(cfg).eval()
+    ids = torch.randint(0, cfg.vocab_size, (2, 32))
+    out = m(ids, labels=ids, return_logits=True)
+    ref = torch.nn.functional.cross_entropy(out.logits[:, :-1].reshape(-1, cfg.vocab_size), ids[:, 1:].reshape(-1))
+    assert abs(out.loss.item() - ref.item()) < 1e-4
+    assert m.head_weight is m.word_embeddings

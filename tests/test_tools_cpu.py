@@ -1,0 +1,133 @@
+"""Golden values of the estimator tools, util helpers, synthetic data, comms logger, launcher,
+bucket assignment and checkpoint resume — everything that needs no GPU and no process group."""
+import os
+import subprocess
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(*args, timeout=300):
+    return subprocess.run([sys.executable, *args], cwd=ROOT, capture_output=True, text=True, timeout=timeout)
+
+
+def test_estimate_nn_memory_golden_values():
+    r = _run("estimate_nn_memory.py")
+    assert "Model Memory: 12,597,248 bytes" in r.stdout, r.stdout + r.stderr
+    assert "Activation Memory: 65,536 bytes" in r.stdout
+
+
+def test_transformer_memory_projection_golden_value():
+    sys.path.insert(0, ROOT)
+    import estimate_transformer_memory as etm
+    total = etm.project_transformer_memory(1, 9216, 72, 4, 512, "adam")
+    assert int(total) == 18_253_430_784
+    b = etm.project_transformer_memory(1, 9216, 72, 4, 512, "adam", breakdown=True)
+    assert (int(b["model"]), int(b["activations"]), int(b["optimizer"])) == (4_077_342_720, 1_944_059_904, 8_154_685_440)
+    from util import format_size
+    assert format_size(total) == "17.0 GB"
+    fused = etm.project_transformer_memory(1, 9216, 72, 4, 512, "adam", fused_attention=True)
+    assert fused < total
+    r = _run("estimate_transformer_memory.py", "--no-measure")
+    assert "Projected total memory usage: 17.0 GB" in r.stdout, r.stdout + r.stderr
+
+
+def test_util_and_synthetic_dataset():
+    sys.path.insert(0, ROOT)
+    from util import format_size, get_device, get_device_count, load_wikitext, synthetic_collator, synthetic_tokenizer
+    from dtds_b200.models import get_config
+    assert format_size(0) == "0B" and format_size(1536) == "1.5 KB"
+    assert get_device() in ("cuda", "cpu", "mps") and get_device_count() >= 1
+    tok = synthetic_tokenizer(get_config("bert-base-cased"))
+    ds = load_wikitext(tok, synthetic_collator(tok, mlm=True)).select(range(32))
+    assert len(ds) == 32 and ds[0]["input_ids"].shape == (512,) and ds[0]["labels"].dtype == torch.int64
+    frac = (ds.labels != -100).float().mean().item()
+    assert 0.10 < frac < 0.20
+    assert (ds.input_ids[ds.labels != -100] == 103).float().mean().item() > 0.6   # ~80 % [MASK]
+    clm = load_wikitext(tok, synthetic_collator(tok, mlm=False), max_length=128).select(range(4))
+    assert torch.equal(clm.input_ids, clm.labels) and clm.input_ids.shape == (4, 128)
+
+
+def test_comms_logger_data_model_and_busbw():
+    from dtds_b200.comm.logger import CommsLogger, calc_bw
+    lg = CommsLogger()
+    lg.configure({"enabled": True, "verbose": False, "prof_all": True, "debug": False})
+    lg.append_host("all_reduce", 1 << 20, 1.0, 8)
+    lg.append_host("all_reduce", 1 << 20, 3.0, 8)
+    rec = lg.comms_dict["all_reduce"][1 << 20]
+    assert rec[0] == 2 and rec[1] == [1.0, 3.0] and len(rec[2]) == 2 and len(rec[3]) == 2
+    alg, bus = calc_bw("all_reduce", 10 ** 9, 1000.0, 8)
+    assert abs(alg - 8.0) < 1e-9 and abs(bus - 8.0 * 2 * 7 / 8) < 1e-9
+    alg, bus = calc_bw("all_gather_into_tensor", 10 ** 9, 1000.0, 4)
+    assert abs(bus - 8.0 * 3 / 4) < 1e-9
+    assert lg.total_latency_ms() == 4.0
+    lg.log_all(print_log=True)
+
+
+def test_bucket_assignment_reverse_order_and_caps():
+    from dtds_b200.parallel.ddp import assign_buckets
+    ps = [torch.nn.Parameter(torch.zeros(n)) for n in (300_000, 100_000, 100_000, 200_000, 50_000)]
+    offs, o = [], 0
+    for p in ps:
+        offs.append(o)
+        o += p.numel()
+    b = assign_buckets(ps, offs, bucket_cap_mb=1.0, elem_size=4, first_bucket_mb=0.25)  # caps: 262144 / 65536 elts
+    assert b[0][0] == [4]                     # small first bucket holds only the last parameter
+    assert b[1][0] == [3] and b[2][0] == [2, 1] and b[3][0] == [0]   # oversize parameter gets its own bucket
+    assert all(lo < hi for _, lo, hi in b)
+
+
+def test_launcher_env_contract_and_failure_propagation(tmp_path):
+    script = tmp_path / "child.py"
+    script.write_text("import os, sys\n"
+                      "assert any(a.startswith('--local_rank=') for a in sys.argv)\n"
+                      "print('R', os.environ['RANK'], os.environ['LOCAL_RANK'], os.environ['WORLD_SIZE'], os.environ['MASTER_ADDR'])\n"
+                      "sys.exit(3 if os.environ['RANK'] == '1' and 'fail' in sys.argv else 0)\n")
+    ok = _run("-m", "dtds_b200.launch", "--nproc-per-node", "2", str(script))
+    assert ok.returncode == 0 and "R 0 0 2 127.0.0.1" in ok.stdout and "R 1 1 2 127.0.0.1" in ok.stdout
+    bad = _run("-m", "dtds_b200.launch", "--nproc-per-node", "2", str(script), "fail")
+    assert bad.returncode == 3
+    from dtds_b200.launch import parse_hostfile
+    hf = tmp_path / "hostfile"
+    hf.write_text("worker-1 slots=4\nworker-2 slots=2  # comment\n")
+    assert parse_hostfile(str(hf)) == {"worker-1": 4, "worker-2": 2}
+
+
+def test_checkpoint_resume_matches_uninterrupted_run(tmp_path):
+    from dtds_b200.models import build_model, get_config
+    from dtds_b200.optim import FusedAdam
+    from dtds_b200.utils.ckpt import load_checkpoint, save_checkpoint
+    cfg = get_config("opt-tiny").replace(hidden_dropout_prob=0.0, num_hidden_layers=1)
+    ids = torch.randint(0, cfg.vocab_size, (2, 16), generator=torch.Generator().manual_seed(0))
+
+    def make():
+        torch.manual_seed(0)
+        m = build_model(cfg)
+        return m, FusedAdam(m.parameters(), lr=1e-2)
+
+    def steps(m, opt, n):
+        out = []
+        for _ in range(n):
+            opt.zero_grad()
+            loss = m(ids, labels=ids).loss
+            loss.backward()
+            opt.step()
+            out.append(loss.item())
+        return out
+
+    m1, o1 = make()
+    full = steps(m1, o1, 6)
+    m2, o2 = make()
+    first = steps(m2, o2, 3)
+    save_checkpoint(str(tmp_path / "ck"), m2, o2, step=3)
+    m3, o3 = make()
+    with torch.no_grad():
+        for p in m3.parameters():
+            p.add_(1.0)   # scramble: the load must restore everything
+    assert load_checkpoint(str(tmp_path / "ck"), m3, o3) == 3
+    rest = steps(m3, o3, 3)
+    assert first + rest == full
+    sd = torch.load(tmp_path / "ck" / "model.pt")
+    assert set(sd.keys()) == set(m1.state_dict().keys())
