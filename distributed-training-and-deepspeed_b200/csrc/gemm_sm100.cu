@@ -40,7 +40,8 @@ struct GemmCfg {
   static constexpr int kStage = kAStage + kBStage;
   static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
   static constexpr int kTmemCols = 2 * BN;  // two accumulator stages
-  static constexpr int kSmemBytes = kStages * kStage + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kStageOut = 8 * 32 * 128;  // epilogue staging: 8 warps x 32 rows x 128 B
+  static constexpr int kSmemBytes = kStages * kStage + kStageOut + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 struct GemmParams {
@@ -58,7 +59,61 @@ struct GemmParams {
   int out_fp32;
   int accumulate;  // D += result
   float alpha;
+  long long* dbg;  // optional [grid][16] clock64 timeline (null in production)
 };
+
+// ---- epilogue row helpers: 32 consecutive columns of one output row, registers only ----------
+template <class F>
+__device__ __forceinline__ void combine_row32(const __nv_bfloat16* __restrict__ src, int nvalid,
+                                              bool full, float (&v)[32], F f) {
+  if (full) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const uint4 u = *reinterpret_cast<const uint4*>(src + g * 8);
+      f(v[g * 8 + 0], bf16_lo(u.x)); f(v[g * 8 + 1], bf16_hi(u.x));
+      f(v[g * 8 + 2], bf16_lo(u.y)); f(v[g * 8 + 3], bf16_hi(u.y));
+      f(v[g * 8 + 4], bf16_lo(u.z)); f(v[g * 8 + 5], bf16_hi(u.z));
+      f(v[g * 8 + 6], bf16_lo(u.w)); f(v[g * 8 + 7], bf16_hi(u.w));
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < nvalid) f(v[j], __bfloat162float(src[j]));
+  }
+}
+__device__ __forceinline__ void store_row32_bf16(__nv_bfloat16* __restrict__ dst, int nvalid, bool full,
+                                                 float (&v)[32], bool accumulate) {
+  if (accumulate) combine_row32(dst, nvalid, full, v, [](float& a, float x) { a += x; });
+  if (full) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+      *reinterpret_cast<uint4*>(dst + g * 8) =
+          make_uint4(pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]), pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]),
+                     pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]));
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < nvalid) dst[j] = __float2bfloat16(v[j]);
+  }
+}
+__device__ __forceinline__ void store_row32_f32(float* __restrict__ dst, int nvalid, bool full,
+                                                float (&v)[32], bool accumulate) {
+  if (full) {
+#pragma unroll
+    for (int g = 0; g < 8; ++g) {
+      float4 o = make_float4(v[g * 4], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+      if (accumulate) {
+        const float4 old = *reinterpret_cast<const float4*>(dst + g * 4);
+        o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+      }
+      *reinterpret_cast<float4*>(dst + g * 4) = o;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (j < nvalid) dst[j] = accumulate ? dst[j] + v[j] : v[j];
+  }
+}
 
 template <int BN, bool A_MN, bool B_MN>
 // 96 registers: 320 threads x 96 leaves room on the SM for a 512-thread, 64-register
@@ -72,7 +127,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + Cfg::kStages * Cfg::kAStage;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStage);
+  uint8_t* s_out = smem + Cfg::kStages * Cfg::kStage;  // per-warp output staging (128B-pitch, XOR swizzle)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_out + Cfg::kStageOut);
   uint64_t* full = bars;
   uint64_t* empty = bars + Cfg::kStages;
   uint64_t* tmem_full = bars + 2 * Cfg::kStages;
@@ -81,6 +137,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  long long* dbg = p.dbg != nullptr ? p.dbg + static_cast<size_t>(blockIdx.x) * 16 : nullptr;
+  if (dbg != nullptr && threadIdx.x == 0) dbg[0] = clock64();
 
   const int num_m = (p.M + kBM - 1) / kBM;
   const int num_n = (p.N + BN - 1) / BN;
@@ -108,6 +166,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (dbg != nullptr && threadIdx.x == 0) dbg[1] = clock64();  // setup done
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -158,6 +217,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
         }
       }
+      if (dbg != nullptr) dbg[2] = clock64();  // all TMA loads issued
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
@@ -175,6 +235,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full[s], ph);
           tc_fence_after();
+          if (dbg != nullptr && it == 0 && kb == 0) dbg[3] = clock64();  // first operands landed
           const uint32_t a_addr = smem_u32(sA + s * Cfg::kAStage);
           const uint32_t b_addr = smem_u32(sB + s * Cfg::kBStage);
 #pragma unroll
@@ -189,6 +250,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
         }
         umma_commit(&tmem_full[as]);  // accumulator complete -> epilogue
+        if (dbg != nullptr && it == 0) dbg[4] = clock64();  // all MMAs of the first tile issued
       }
     }
   } else {
@@ -196,6 +258,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int q = warp & 3;          // TMEM lane quadrant this warp may access
     const int chalf = (warp - 2) >> 2;  // which half of the tile's column chunks this warp owns
     constexpr int kChunksPerWarp = BN / 64;
+    constexpr int kGroup = kChunksPerWarp >= 2 ? 2 : 1;  // chunks staged together (64 or 32 columns)
+    constexpr int kPieces = kGroup * 4;                   // 16-byte pieces per staged row
+    uint8_t* stage = s_out + (warp - 2) * (32 * 128);
+    // Staged path: bf16 output, plain overwrite.  Rows go through shared memory so that one warp
+    // store instruction writes kPieces*16 contiguous bytes of 32/kPieces rows (full cache lines)
+    // instead of 16 bytes of 32 different rows.
+    const bool can_stage = !p.out_fp32 && !p.accumulate;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const int m0 = (tile % num_m) * kBM;
@@ -204,130 +273,103 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t aph = (it >> 1) & 1;
       mbar_wait(&tmem_full[as], aph);
       tc_fence_after();
+      if (dbg != nullptr && it == 0 && threadIdx.x == 64) dbg[5] = clock64();  // accumulator ready
       const int row = m0 + q * 32 + lane;
       const bool row_ok = row < p.M;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
 #pragma unroll 1
-      for (int cc = 0; cc < kChunksPerWarp; ++cc) {
-        const int c = chalf * kChunksPerWarp + cc;
-        const int col0 = n0 + c * 32;
-        if (col0 >= p.N) break;  // warp-uniform
-        uint32_t r[32];
-        tmem_ld_32x32(t_row + c * 32, r);
-        tmem_ld_wait();
-        if (!row_ok) continue;
-        float v[32];
+      for (int g0 = 0; g0 < kChunksPerWarp; g0 += kGroup) {
+        const int gcol0 = n0 + (chalf * kChunksPerWarp + g0) * 32;
+        if (gcol0 >= p.N) break;  // warp-uniform
+        const bool staged = can_stage && (gcol0 + kGroup * 32 <= p.N);
+#pragma unroll 1   // one copy of the chunk code: every CTA runs it once or twice, so its
+                   // instruction-cache footprint (cold fetches) is part of the latency
+        for (int h = 0; h < kGroup; ++h) {
+          const int c = chalf * kChunksPerWarp + g0 + h;
+          const int col0 = n0 + c * 32;
+          if (col0 >= p.N) break;  // warp-uniform
+          uint32_t r[32];
+          tmem_ld_32x32(t_row + c * 32, r);
+          tmem_ld_wait();
+          if (dbg != nullptr && it == 0 && threadIdx.x == 64 && g0 == 0) dbg[8 + h * 3] = clock64();
+          // Everything below indexes v[] with compile-time constants only (fully unrolled, tails
+          // handled by predicates) so the 32 accumulator values stay in registers.
+          float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
-        const bool full_chunk = (col0 + 32 <= p.N);
-        if (p.bias != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (full_chunk || col0 + j < p.N) v[j] += __bfloat162float(__ldg(p.bias + col0 + j));
-        }
-        if (p.pre_out != nullptr) {
-          __nv_bfloat16* dst = p.pre_out + static_cast<size_t>(row) * p.ldd + col0;
-          if (full_chunk) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint4 o = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
-                                   pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
-              *reinterpret_cast<uint4*>(dst + j) = o;
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+          const bool full_chunk = (col0 + 32 <= p.N);
+          const int nvalid = full_chunk ? 32 : p.N - col0;
+          const size_t out_off = static_cast<size_t>(row_ok ? row : 0) * p.ldd + col0;
+          if (p.bias != nullptr)
+            combine_row32(p.bias + col0, nvalid, full_chunk, v, [](float& a, float x) { a += x; });
+          if (p.pre_out != nullptr && row_ok)
+            store_row32_bf16(p.pre_out + out_off, nvalid, full_chunk, v, false);
+          if (p.dact_in != nullptr) {
+            if (row_ok) {
+              const __nv_bfloat16* dsrc = p.dact_in + static_cast<size_t>(row) * p.ld_dact + col0;
+              if (p.act == ACT_GELU_ERF)
+                combine_row32(dsrc, nvalid, full_chunk, v, [](float& a, float x) { a *= gelu_erf_grad(x); });
+              else if (p.act == ACT_RELU)
+                combine_row32(dsrc, nvalid, full_chunk, v, [](float& a, float x) { a = x > 0.f ? a : 0.f; });
+              else if (p.act == ACT_GELU_TANH)
+                combine_row32(dsrc, nvalid, full_chunk, v, [](float& a, float x) { a *= gelu_tanh_grad(x); });
             }
-          } else {
-            for (int j = 0; j < 32 && col0 + j < p.N; ++j) dst[j] = __float2bfloat16(v[j]);
+          } else if (p.act == ACT_GELU_ERF) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+          } else if (p.act == ACT_RELU) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+          } else if (p.act == ACT_GELU_TANH) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = gelu_tanh(v[j]);
           }
-        }
-        if (p.act != ACT_NONE && p.dact_in == nullptr) {
+          if (p.residual != nullptr && row_ok)
+            combine_row32(p.residual + static_cast<size_t>(row) * p.ld_res + col0, nvalid, full_chunk, v,
+                          [](float& a, float x) { a += x; });
+          if (dbg != nullptr && it == 0 && threadIdx.x == 64 && g0 == 0) dbg[9 + h * 3] = clock64();
+          if (staged) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act);
-        }
-        if (p.dact_in != nullptr) {
-          const __nv_bfloat16* src = p.dact_in + static_cast<size_t>(row) * p.ld_dact + col0;
-          if (full_chunk) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              const uint4 u = *reinterpret_cast<const uint4*>(src + j);
-              const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-              for (int t = 0; t < 4; ++t) {
-                v[j + 2 * t] *= act_grad(bf16_lo(w[t]), p.act);
-                v[j + 2 * t + 1] *= act_grad(bf16_hi(w[t]), p.act);
-              }
+            for (int g = 0; g < 4; ++g) {
+              const int piece = h * 4 + g;
+              *reinterpret_cast<uint4*>(stage + lane * 128 + ((piece ^ (lane & 7)) << 4)) =
+                  make_uint4(pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]), pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]),
+                             pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]), pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]));
             }
-          } else {
-            for (int j = 0; j < 32 && col0 + j < p.N; ++j)
-              v[j] *= act_grad(__bfloat162float(src[j]), p.act);
+          } else if (row_ok) {
+            if (p.out_fp32)
+              store_row32_f32(reinterpret_cast<float*>(p.D) + out_off, nvalid, full_chunk, v, p.accumulate != 0);
+            else
+              store_row32_bf16(reinterpret_cast<__nv_bfloat16*>(p.D) + out_off, nvalid, full_chunk, v,
+                               p.accumulate != 0);
           }
+          if (dbg != nullptr && it == 0 && threadIdx.x == 64 && g0 == 0) dbg[10 + h * 3] = clock64();
         }
-        if (p.residual != nullptr) {
-          const __nv_bfloat16* src = p.residual + static_cast<size_t>(row) * p.ld_res + col0;
-          if (full_chunk) {
+        if (staged) {
+          __syncwarp();
+          constexpr int kRowsPerInstr = 32 / kPieces;
+          const int piece = lane % kPieces;
+          __nv_bfloat16* dbase = reinterpret_cast<__nv_bfloat16*>(p.D) + gcol0 + piece * 8;
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              const uint4 u = *reinterpret_cast<const uint4*>(src + j);
-              const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-              for (int t = 0; t < 4; ++t) {
-                v[j + 2 * t] += bf16_lo(w[t]);
-                v[j + 2 * t + 1] += bf16_hi(w[t]);
-              }
-            }
-          } else {
-            for (int j = 0; j < 32 && col0 + j < p.N; ++j) v[j] += __bfloat162float(src[j]);
+          for (int i = 0; i < kPieces; ++i) {
+            const int rr = i * kRowsPerInstr + lane / kPieces;
+            const uint4 x = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((piece ^ (rr & 7)) << 4));
+            const int grow = m0 + q * 32 + rr;
+            if (grow < p.M) *reinterpret_cast<uint4*>(dbase + static_cast<size_t>(grow) * p.ldd) = x;
           }
-        }
-        if (p.out_fp32) {
-          float* dst = reinterpret_cast<float*>(p.D) + static_cast<size_t>(row) * p.ldd + col0;
-          if (full_chunk) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-              if (p.accumulate) {
-                const float4 old = *reinterpret_cast<const float4*>(dst + j);
-                o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
-              }
-              *reinterpret_cast<float4*>(dst + j) = o;
-            }
-          } else {
-            for (int j = 0; j < 32 && col0 + j < p.N; ++j)
-              dst[j] = p.accumulate ? dst[j] + v[j] : v[j];
-          }
-        } else {
-          __nv_bfloat16* dst =
-              reinterpret_cast<__nv_bfloat16*>(p.D) + static_cast<size_t>(row) * p.ldd + col0;
-          if (full_chunk) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              if (p.accumulate) {
-                const uint4 u = *reinterpret_cast<const uint4*>(dst + j);
-                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                  v[j + 2 * t] += bf16_lo(w[t]);
-                  v[j + 2 * t + 1] += bf16_hi(w[t]);
-                }
-              }
-              uint4 o = make_uint4(pack_bf16x2(v[j], v[j + 1]), pack_bf16x2(v[j + 2], v[j + 3]),
-                                   pack_bf16x2(v[j + 4], v[j + 5]), pack_bf16x2(v[j + 6], v[j + 7]));
-              *reinterpret_cast<uint4*>(dst + j) = o;
-            }
-          } else {
-            for (int j = 0; j < 32 && col0 + j < p.N; ++j) {
-              const float o = p.accumulate ? v[j] + __bfloat162float(dst[j]) : v[j];
-              dst[j] = __float2bfloat16(o);
-            }
-          }
+          __syncwarp();
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[as]);
+      if (dbg != nullptr && it == 0 && threadIdx.x == 64) dbg[6] = clock64();  // first tile stored
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if (dbg != nullptr && threadIdx.x == 0) dbg[7] = clock64();
   tc_fence_after();
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
 }
@@ -456,6 +498,15 @@ static int pick_block_n(int M, int N, int K, int requested) {
 
 using namespace dtds;
 
+static long long* g_gemm_dbg = nullptr;
+// Development aid: when set, every GEMM CTA writes 8 clock64() stamps (start, setup done, loads
+// issued, first operands landed, MMAs issued, accumulator ready, first tile stored, end) to
+// buf[blockIdx.x * 8 ...].  Pass NULL to switch it off.
+extern "C" int dtds_gemm_set_debug_buffer(long long* buf) {
+  g_gemm_dbg = buf;
+  return 0;
+}
+
 extern "C" int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const void* bias,
                                  const void* residual, void* pre_out, const void* dact_in, int M,
                                  int N, int K, int lda, int ldb, int ldd, int ld_res, int ld_dact,
@@ -495,6 +546,7 @@ extern "C" int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const vo
   p.M = M; p.N = N; p.K = K;
   p.ldd = ldd; p.ld_res = ld_res > 0 ? ld_res : ldd; p.ld_dact = ld_dact > 0 ? ld_dact : ldd;
   p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate; p.alpha = alpha;
+  p.dbg = g_gemm_dbg;
 
 #define DTDS_DISPATCH(BN_)                                                                     \
   if (bn == BN_) {                                                                             \

@@ -43,6 +43,8 @@ int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const void* bias,
                       int b_mn_major, int act, int out_fp32, int accumulate, float alpha,
                       int block_n, int max_ctas, const void* ready_flags, unsigned ready_epoch,
                       int rows_per_flag, cudaStream_t stream);
+/* Development aid: per-CTA clock64() timeline of the GEMM kernel into buf[grid][8]; NULL = off. */
+int dtds_gemm_set_debug_buffer(long long* buf);
 
 /* ---- LayerNorm (+dropout +residual), activations, dropout, softmax, column sums, MSE
  *      (ATen kernels behind model/transformer.py:36,43-53; BERT post-LN blocks) ------------- */
