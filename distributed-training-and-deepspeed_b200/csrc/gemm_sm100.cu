@@ -20,8 +20,8 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <cstring>
 #include <mutex>
-#include <unordered_map>
 
 #include "common.cuh"
 #include "dtds_b200.h"
@@ -32,6 +32,8 @@ namespace dtds {
 constexpr int kBM = 128;
 constexpr int kBK = 64;
 constexpr int kGemmThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps
+constexpr int kFetchThreads = 128;  // + 4 fetch warps in the all-gather fused variant
+constexpr int kMaxFetchSegs = 16;
 
 template <int BN>
 struct GemmCfg {
@@ -60,7 +62,39 @@ struct GemmParams {
   int accumulate;  // D += result
   float alpha;
   long long* dbg;  // optional [grid][16] clock64 timeline (null in production)
+  // ---- all-gather fused mode (ZeRO-3): operand B is assembled by this kernel's fetch warps out
+  // of the owners' parameter shards (peer loads over NVLink) while the tiles that are already
+  // complete are being multiplied.
+  const char* seg_src[kMaxFetchSegs];             // source of segment i (peer or local address)
+  unsigned long long seg_begin[kMaxFetchSegs + 1];  // byte offset in B where segment i starts
+  char* fetch_dst;                                // local full copy of B
+  uint32_t* fetch_flags;                          // one arrival flag per chunk (== ready_flags)
+  unsigned long long fetch_total;                 // bytes of B
+  unsigned int fetch_chunk;                       // bytes per chunk (multiple of 16)
+  int fetch_nseg;
+  int flags_on_k;                                 // flags index rows of B along K (dgrad) not N
 };
+
+// Spins (bounded) until flags[f0..f1] have reached `epoch`, then fences generic -> async proxy.
+__device__ __forceinline__ void wait_ready_flags(const uint32_t* flags, int f0, int f1, uint32_t epoch) {
+  for (int f = f0; f <= f1; ++f) {
+    uint32_t spins = 0, v;
+    do {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + f) : "memory");
+      if (++spins > DTDS_SPIN_LIMIT) {
+        printf("[dtds] gemm: ready flag %d stuck at %u (want %u)\n", f, v, epoch);
+        __trap();
+      }
+    } while (v < epoch);
+  }
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
+__device__ __forceinline__ uint4 ld_sys_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
 
 // ---- epilogue row helpers: 32 consecutive columns of one output row, registers only ----------
 template <class F>
@@ -115,7 +149,7 @@ __device__ __forceinline__ void store_row32_f32(float* __restrict__ dst, int nva
   }
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool FETCH>
 // 96 registers: 320 threads x 96 leaves room on the SM for a 512-thread, 64-register
 // communication block (overlapped gradient-bucket all-reduce) next to this persistent CTA.
 __global__ void __maxnreg__(96)
@@ -176,26 +210,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m0 = (tile % num_m) * kBM;
         const int n0 = (tile / num_m) * BN;
-        if (p.ready_flags != nullptr) {
-          // All-gather fused mode: B rows [n0, n0+BN) were written by copy CTAs (possibly of
-          // another kernel on a side stream); wait for the arrival flag(s) covering them, then
-          // order the generic-proxy writes before our async-proxy (TMA) reads.
-          const int f0 = n0 / p.rows_per_flag;
+        if (p.ready_flags != nullptr && !p.flags_on_k) {
+          // All-gather fused mode: B rows [n0, n0+BN) are written by fetch warps (of any CTA of
+          // this grid, or by an earlier kernel); wait for the arrival flag(s) covering them, then
+          // order those generic-proxy writes before our async-proxy (TMA) reads.
           const int n_last = min(n0 + BN, p.N) - 1;
-          const int f1 = n_last / p.rows_per_flag;
-          for (int f = f0; f <= f1; ++f) {
-            uint32_t spins = 0, v;
-            do {
-              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p.ready_flags + f));
-              if (++spins > DTDS_SPIN_LIMIT) {
-                printf("[dtds] gemm: ready flag %d stuck at %u (want %u)\n", f, v, p.ready_epoch);
-                __trap();
-              }
-            } while (v < p.ready_epoch);
-          }
-          asm volatile("fence.proxy.async;" ::: "memory");
+          wait_ready_flags(p.ready_flags, n0 / p.rows_per_flag, n_last / p.rows_per_flag, p.ready_epoch);
         }
         for (int kb = 0; kb < num_kb; ++kb) {
+          if (p.ready_flags != nullptr && p.flags_on_k) {  // dgrad: B rows are indexed by k
+            const int k_last = min(kb * kBK + kBK, p.K) - 1;
+            wait_ready_flags(p.ready_flags, kb * kBK / p.rows_per_flag, k_last / p.rows_per_flag,
+                             p.ready_epoch);
+          }
           mbar_wait(&empty[s], ph ^ 1);
           mbar_expect_tx(&full[s], Cfg::kStage);
           uint8_t* a_dst = sA + s * Cfg::kAStage;
@@ -253,7 +280,44 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (dbg != nullptr && it == 0) dbg[4] = clock64();  // all MMAs of the first tile issued
       }
     }
-  } else {
+  } else if (FETCH && warp >= 10) {
+    // ------------------------------------------------------------------ fetch warps (all-gather)
+    // Chunk c of B (fetch_chunk bytes) is assembled by CTA (c mod grid): 128 threads stream it
+    // from the owning ranks' shard buffers with 4 independent 128-bit peer loads in flight per
+    // thread, then publish the chunk's arrival flag with release semantics.
+    const int ft = threadIdx.x - kGemmThreads;
+    const unsigned long long nchunks = (p.fetch_total + p.fetch_chunk - 1) / p.fetch_chunk;
+    for (unsigned long long c = blockIdx.x; c < nchunks; c += gridDim.x) {
+      const unsigned long long b0 = c * p.fetch_chunk;
+      const unsigned long long b1 = min(p.fetch_total, b0 + p.fetch_chunk);
+      for (int sg = 0; sg < p.fetch_nseg; ++sg) {
+        const unsigned long long lo = max(b0, p.seg_begin[sg]);
+        const unsigned long long hi = min(b1, p.seg_begin[sg + 1]);
+        if (lo >= hi) continue;
+        const char* src = p.seg_src[sg] + (lo - p.seg_begin[sg]);
+        char* dst = p.fetch_dst + lo;
+        const unsigned long long nv = (hi - lo) >> 4;
+        unsigned long long v = ft;
+        for (; v + 3 * kFetchThreads < nv; v += 4 * kFetchThreads) {
+          const uint4 x0 = ld_sys_v4(src + (v << 4));
+          const uint4 x1 = ld_sys_v4(src + ((v + kFetchThreads) << 4));
+          const uint4 x2 = ld_sys_v4(src + ((v + 2 * kFetchThreads) << 4));
+          const uint4 x3 = ld_sys_v4(src + ((v + 3 * kFetchThreads) << 4));
+          *reinterpret_cast<uint4*>(dst + (v << 4)) = x0;
+          *reinterpret_cast<uint4*>(dst + ((v + kFetchThreads) << 4)) = x1;
+          *reinterpret_cast<uint4*>(dst + ((v + 2 * kFetchThreads) << 4)) = x2;
+          *reinterpret_cast<uint4*>(dst + ((v + 3 * kFetchThreads) << 4)) = x3;
+        }
+        for (; v < nv; v += kFetchThreads)
+          *reinterpret_cast<uint4*>(dst + (v << 4)) = ld_sys_v4(src + (v << 4));
+      }
+      __threadfence();
+      named_bar_sync(3, kFetchThreads);
+      if (ft == 0)
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.fetch_flags + c), "r"(p.ready_epoch)
+                     : "memory");
+    }
+  } else if (warp >= 2 && warp < 10) {
     // ------------------------------------------------------------------ epilogue warps
     const int q = warp & 3;          // TMEM lane quadrant this warp may access
     const int chalf = (warp - 2) >> 2;  // which half of the tile's column chunks this warp owns
@@ -442,11 +506,11 @@ int sm_count() {
   return cached[dev];
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool FETCH = false>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
                        int max_ctas, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, FETCH>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -458,8 +522,8 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   const int num_tiles = ((p.M + kBM - 1) / kBM) * ((p.N + BN - 1) / BN);
   int grid = sm_count();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
-  if (num_tiles < grid) grid = num_tiles;
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(tmA, tmB, p);
+  if (num_tiles < grid && !FETCH) grid = num_tiles;  // fetch mode keeps every SM pulling chunks
+  kern<<<grid, kGemmThreads + (FETCH ? kFetchThreads : 0), Cfg::kSmemBytes, stream>>>(tmA, tmB, p);
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }
@@ -507,13 +571,20 @@ extern "C" int dtds_gemm_set_debug_buffer(long long* buf) {
   return 0;
 }
 
-extern "C" int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const void* bias,
-                                 const void* residual, void* pre_out, const void* dact_in, int M,
-                                 int N, int K, int lda, int ldb, int ldd, int ld_res, int ld_dact,
-                                 int a_mn_major, int b_mn_major, int act, int out_fp32,
-                                 int accumulate, float alpha, int block_n, int max_ctas,
-                                 const void* ready_flags, unsigned ready_epoch, int rows_per_flag,
-                                 cudaStream_t stream) {
+struct FetchSpec {
+  const unsigned long long* seg_src;
+  const unsigned long long* seg_begin;  // nseg + 1 entries
+  int nseg;
+  unsigned chunk_bytes;
+  int flags_on_k;
+};
+
+static int gemm_impl(const void* A, const void* B, void* D, const void* bias, const void* residual,
+                     void* pre_out, const void* dact_in, int M, int N, int K, int lda, int ldb, int ldd,
+                     int ld_res, int ld_dact, int a_mn_major, int b_mn_major, int act, int out_fp32,
+                     int accumulate, float alpha, int block_n, int max_ctas, const void* ready_flags,
+                     unsigned ready_epoch, int rows_per_flag, const FetchSpec* fetch,
+                     cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) ||
       (reinterpret_cast<uintptr_t>(D) & 15) || (lda % 8) || (ldb % 8) ||
@@ -535,6 +606,7 @@ extern "C" int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const vo
   if (rc) return rc;
 
   GemmParams p;
+  memset(&p, 0, sizeof(p));
   p.D = D;
   p.bias = static_cast<const __nv_bfloat16*>(bias);
   p.residual = static_cast<const __nv_bfloat16*>(residual);
@@ -547,19 +619,79 @@ extern "C" int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const vo
   p.ldd = ldd; p.ld_res = ld_res > 0 ? ld_res : ldd; p.ld_dact = ld_dact > 0 ? ld_dact : ldd;
   p.act = act; p.out_fp32 = out_fp32; p.accumulate = accumulate; p.alpha = alpha;
   p.dbg = g_gemm_dbg;
+  if (fetch != nullptr) {
+    if (fetch->nseg < 1 || fetch->nseg > kMaxFetchSegs || (fetch->chunk_bytes % 16) || ready_flags == nullptr) {
+      fprintf(stderr, "[dtds] gemm(all-gather): need 1..%d segments, a 16-byte chunk size and flags\n",
+              kMaxFetchSegs);
+      return -5;
+    }
+    for (int i = 0; i < fetch->nseg; ++i) p.seg_src[i] = reinterpret_cast<const char*>(fetch->seg_src[i]);
+    for (int i = 0; i <= fetch->nseg; ++i) p.seg_begin[i] = fetch->seg_begin[i];
+    p.fetch_nseg = fetch->nseg;
+    p.fetch_dst = static_cast<char*>(const_cast<void*>(B));
+    p.fetch_flags = static_cast<uint32_t*>(const_cast<void*>(ready_flags));
+    p.fetch_total = fetch->seg_begin[fetch->nseg];
+    p.fetch_chunk = fetch->chunk_bytes;
+    p.flags_on_k = fetch->flags_on_k;
+  }
+  const bool f = fetch != nullptr;
 
-#define DTDS_DISPATCH(BN_)                                                                     \
-  if (bn == BN_) {                                                                             \
-    if (!a_mn_major && !b_mn_major) return launch_gemm<BN_, false, false>(tmA, tmB, p, max_ctas, stream); \
-    if (!a_mn_major && b_mn_major)  return launch_gemm<BN_, false, true>(tmA, tmB, p, max_ctas, stream);  \
-    if (a_mn_major && !b_mn_major)  return launch_gemm<BN_, true, false>(tmA, tmB, p, max_ctas, stream);  \
-    return launch_gemm<BN_, true, true>(tmA, tmB, p, max_ctas, stream);                        \
+#define DTDS_DISPATCH(BN_)                                                                          \
+  if (bn == BN_) {                                                                                  \
+    if (!a_mn_major && !b_mn_major)                                                                 \
+      return f ? launch_gemm<BN_, false, false, true>(tmA, tmB, p, max_ctas, stream)                \
+               : launch_gemm<BN_, false, false, false>(tmA, tmB, p, max_ctas, stream);              \
+    if (!a_mn_major && b_mn_major)                                                                  \
+      return f ? launch_gemm<BN_, false, true, true>(tmA, tmB, p, max_ctas, stream)                 \
+               : launch_gemm<BN_, false, true, false>(tmA, tmB, p, max_ctas, stream);               \
+    if (f) { fprintf(stderr, "[dtds] gemm(all-gather): operand A must be K-major\n"); return -6; } \
+    if (a_mn_major && !b_mn_major) return launch_gemm<BN_, true, false, false>(tmA, tmB, p, max_ctas, stream); \
+    return launch_gemm<BN_, true, true, false>(tmA, tmB, p, max_ctas, stream);                      \
   }
   DTDS_DISPATCH(64)
   DTDS_DISPATCH(128)
   DTDS_DISPATCH(256)
 #undef DTDS_DISPATCH
   return -4;
+}
+
+extern "C" int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const void* bias,
+                                 const void* residual, void* pre_out, const void* dact_in, int M,
+                                 int N, int K, int lda, int ldb, int ldd, int ld_res, int ld_dact,
+                                 int a_mn_major, int b_mn_major, int act, int out_fp32,
+                                 int accumulate, float alpha, int block_n, int max_ctas,
+                                 const void* ready_flags, unsigned ready_epoch, int rows_per_flag,
+                                 cudaStream_t stream) {
+  return gemm_impl(A, B, D, bias, residual, pre_out, dact_in, M, N, K, lda, ldb, ldd, ld_res, ld_dact,
+                   a_mn_major, b_mn_major, act, out_fp32, accumulate, alpha, block_n, max_ctas,
+                   ready_flags, ready_epoch, rows_per_flag, nullptr, stream);
+}
+
+// ZeRO-3 parameter all-gather fused with the consuming GEMM.  B (the weight, [N,K] K-major for
+// forward, consumed MN-major for dgrad) is NOT complete in memory when the kernel starts: it is
+// described by `nseg` byte segments (seg_begin[i] .. seg_begin[i+1]) whose sources are the
+// owners' shard buffers (peer-mapped addresses).  Fetch warps inside the GEMM kernel copy them
+// into `B_local` chunk by chunk (`chunk_bytes`, a whole number of B rows) and raise flags[chunk]
+// to `epoch`; the TMA producer of every CTA waits for the flags of the rows it needs, so tiles
+// start as soon as their part of the weight has arrived and the NVLink transfer overlaps the
+// tensor-core work tile by tile.  `flags` must hold one uint32 per chunk and `epoch` must be
+// larger than any value used with these flags before (monotonic; no reset between calls).
+extern "C" int dtds_gemm_bf16_allgather(const void* A, void* B_local, void* D, const void* bias,
+                                        const void* residual, int M, int N, int K, int lda, int ldb,
+                                        int ldd, int ld_res, int b_mn_major, int act, int block_n,
+                                        const unsigned long long* seg_src,
+                                        const unsigned long long* seg_begin, int nseg,
+                                        unsigned chunk_bytes, void* flags, unsigned epoch,
+                                        cudaStream_t stream) {
+  const size_t row_bytes = static_cast<size_t>(ldb) * 2;
+  if (chunk_bytes == 0 || chunk_bytes % row_bytes != 0) {
+    fprintf(stderr, "[dtds] gemm(all-gather): chunk_bytes must be a whole number of B rows\n");
+    return -7;
+  }
+  FetchSpec fs{seg_src, seg_begin, nseg, chunk_bytes, b_mn_major ? 1 : 0};
+  const int rows_per_flag = static_cast<int>(chunk_bytes / row_bytes);
+  return gemm_impl(A, B_local, D, bias, residual, nullptr, nullptr, M, N, K, lda, ldb, ldd, ld_res, 0, 0,
+                   b_mn_major, act, 0, 0, 1.0f, block_n, 0, flags, epoch, rows_per_flag, &fs, stream);
 }
 
 extern "C" int dtds_gemm_bf16(const void* A, const void* B, void* D, const void* bias, int M, int N,

@@ -86,6 +86,10 @@ class SelfAttention(nn.Module):
         self.hidden, self.heads, self.p_drop, self.causal = hidden, heads, p_drop, causal
         self.qkv = Linear(hidden, 3 * hidden, bias=bias)
         self.out = Linear(hidden, hidden, bias=bias)
+        # ZeRO-3 may leave this weight un-gathered and let the QKV GEMM pull it from the owners'
+        # shards itself (all-gather fused with the first consuming GEMM of the block): it is only
+        # ever read through Fn.linear, which knows how to do that.
+        self.qkv.weight._ag_ok = True
         # fp32 slopes, kept out of the buffer registry so `.to(bfloat16)` cannot down-cast them
         # (the attention kernel reads them as float*)
         self._alibi_slopes = alibi_slopes(heads) if alibi else None

@@ -110,9 +110,13 @@ _KERNELS_PER_CALL = {"dtds_cross_entropy": 2, "dtds_layernorm_bwd": 2,
                      "dtds_attention_bwd": 3, "dtds_adam_flat": 2}
 
 
+call_counts: dict = {}  # C entry point name -> number of calls (tests assert on fused paths)
+
+
 def check(rc: int, what: str) -> None:
     global _launches
     _launches += _KERNELS_PER_CALL.get(what, 1)
+    call_counts[what] = call_counts.get(what, 0) + 1
     if rc != 0:
         raise NativeLibraryError(f"{what} failed with code {rc} (see stderr for details)")
 

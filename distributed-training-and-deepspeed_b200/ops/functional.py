@@ -98,7 +98,14 @@ class LinearFn(torch.autograd.Function):
         need_pre = act != ACT_NONE and any(ctx.needs_input_grad)
         pre = torch.empty(x2.shape[0], N, dtype=x2.dtype, device=x2.device) if need_pre else None
         res2 = residual.reshape(-1, N) if residual is not None else None
-        y = K.gemm(x2, weight, bias=bias, act=act, residual=res2, pre_out=pre)
+        if getattr(weight, "_ag_pending", False):
+            # ZeRO-3: the weight has not been gathered; the GEMM kernel assembles it from the
+            # owners' shards while it computes (all-gather fused with the consuming GEMM).
+            assert pre is None, "fused all-gather GEMM does not save pre-activations"
+            y = K.gemm_allgather(x2, weight.data, weight._ag_spec, bias=bias, act=act, residual=res2)
+            weight._ag_pending = False
+        else:
+            y = K.gemm(x2, weight, bias=bias, act=act, residual=res2, pre_out=pre)
         ctx.save_for_backward(x2, weight, bias, pre)
         ctx.act = act
         ctx.has_res = residual is not None
@@ -116,7 +123,11 @@ class LinearFn(torch.autograd.Function):
         du = K.act_bwd(dy2, pre, ctx.act) if ctx.act != ACT_NONE else dy2
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = K.gemm(du, weight, b_mn_major=True).view(ctx.in_shape)
+            if getattr(weight, "_ag_pending", False):   # ZeRO-3 re-gather fused with the dgrad GEMM
+                dx = K.gemm_allgather(du, weight.data, weight._ag_spec, b_mn_major=True).view(ctx.in_shape)
+                weight._ag_pending = False
+            else:
+                dx = K.gemm(du, weight, b_mn_major=True).view(ctx.in_shape)
         dw = _wgrad(du, x2, weight) if ctx.needs_input_grad[1] else None
         db = _bgrad(du, bias) if (bias is not None and ctx.needs_input_grad[2]) else None
         return dx, dw, db, None, dres

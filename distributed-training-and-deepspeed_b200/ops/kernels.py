@@ -424,3 +424,54 @@ def attention_bwd(qkv, out, dout, lse, B, S, heads, *, scale, causal=False, key_
         float(scale), int(causal), float(p_drop), int(seed), _seed_ptr(), _lib.stream_ptr())
     _lib.check(rc, "dtds_attention_bwd")
     return dqkv
+
+
+# ------------------------------------------------------------ all-gather fused GEMM (ZeRO-3)
+class GatherSpec:
+    """Where the pieces of a sharded weight live.
+
+    ``segments`` = [(source_address, nbytes), ...] in the order they appear in the weight's
+    memory; sources are addresses valid in THIS process (local or peer-mapped symmetric memory).
+    ``flags`` holds one uint32 per chunk and is reused across calls with a growing ``epoch``."""
+
+    def __init__(self, segments, total_bytes, device, chunk_rows, row_bytes):
+        import ctypes
+        assert 1 <= len(segments) <= 16, "at most 16 source segments"
+        assert sum(n for _, n in segments) == total_bytes
+        self.nseg = len(segments)
+        self.src = (ctypes.c_ulonglong * self.nseg)(*[a for a, _ in segments])
+        begins, off = [0], 0
+        for _, n in segments:
+            off += n
+            begins.append(off)
+        self.begin = (ctypes.c_ulonglong * (self.nseg + 1))(*begins)
+        self.chunk_bytes = chunk_rows * row_bytes
+        nchunks = (total_bytes + self.chunk_bytes - 1) // self.chunk_bytes
+        self.flags = torch.zeros(nchunks, dtype=torch.int32, device=device)
+        self.epoch = 0
+
+
+def gemm_allgather(a, w_local, spec: GatherSpec, *, b_mn_major=False, bias=None, act=ACT_NONE,
+                   residual=None, out=None, block_n=0):
+    """out = act(a · Wᵀ + bias) (+ residual) (or a · W when b_mn_major) where W is assembled into
+    `w_local` ([N, K], K contiguous) by the kernel itself from `spec`'s segments while it runs."""
+    assert _lib.use_native(a) and a.dtype == torch.bfloat16
+    Nw, Kw = w_local.shape
+    if b_mn_major:
+        M, K = a.shape
+        assert K == Nw
+        N = Kw
+    else:
+        M, K = a.shape
+        assert K == Kw
+        N = Nw
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=a.device)
+    spec.epoch += 1
+    rc = _lib.lib().dtds_gemm_bf16_allgather(
+        a.data_ptr(), w_local.data_ptr(), out.data_ptr(), _lib.ptr(bias), _lib.ptr(residual), M, N, K,
+        a.stride(0), w_local.stride(0), out.stride(0), residual.stride(0) if residual is not None else 0,
+        int(b_mn_major), int(act), int(block_n), spec.src, spec.begin, spec.nseg, spec.chunk_bytes,
+        spec.flags.data_ptr(), spec.epoch, _lib.stream_ptr())
+    _lib.check(rc, "dtds_gemm_bf16_allgather")
+    return out

@@ -29,11 +29,12 @@ from ..ops import _lib
 
 
 class _Block:
-    __slots__ = ("name", "module", "params", "buckets", "live", "event")
+    __slots__ = ("name", "module", "params", "buckets", "live", "event", "lead")
 
     def __init__(self, name, module, params):
         self.name, self.module, self.params = name, module, params
         self.buckets, self.live, self.event = [], False, None
+        self.lead = None  # parameter whose gather is fused into its consuming GEMM
 
 
 class Zero3ParamManager:
@@ -82,6 +83,15 @@ class Zero3ParamManager:
                 b = bucket_of[id(p)]
                 seen[b.index] = b
             blk.buckets = list(seen.values())
+        # all-gather fused with the first consuming GEMM: one flagged Linear weight per block
+        self.fuse_gather = self.custom and bool(engine.config.get("zero_optimization", {}).get(
+            "fuse_allgather_gemm", True))
+        if self.fuse_gather:
+            for blk in self.blocks:
+                for p in blk.params:
+                    if getattr(p, "_ag_ok", False) and p.dim() == 2 and (p._orig_shape[1] * 2) % 16 == 0:
+                        blk.lead = p
+                        break
         # ---- release the full replica: from here on parameters point at per-block gather buffers
         self._full_released = False
         self._side = torch.cuda.Stream(self.dev) if self.dev.type == "cuda" else None
@@ -126,8 +136,22 @@ class Zero3ParamManager:
         return self.shards.numel() * self.shards.element_size()
 
     # ------------------------------------------------------------------------------------
-    def _gather_bucket(self, b) -> torch.Tensor:
-        """Full copy of bucket `b` assembled from all ranks' shards (transient)."""
+    def _segments(self, b, lo: int, hi: int):
+        """(source address, byte offset inside bucket b, nbytes) pieces covering flat elements
+        [lo, hi) of bucket b, in memory order, one piece per owning rank."""
+        esz = self.shards.element_size()
+        out = []
+        for r in range(self.world):
+            s0, s1 = b.lo + r * b.per, b.lo + (r + 1) * b.per
+            a, z = max(lo, s0), min(hi, s1)
+            if a < z:
+                src = self.shard_buf.ptrs[r] + (b.state_off + (a - s0)) * esz
+                out.append((src, (a - b.lo) * esz, (z - a) * esz))
+        return out
+
+    def _gather_bucket(self, b, skip=None) -> torch.Tensor:
+        """Full copy of bucket `b` assembled from all ranks' shards (transient).  `skip` = flat
+        element range [lo, hi) left for a fused all-gather GEMM to fill."""
         f = self.flat
         n = b.hi - b.lo
         full = torch.empty(n, dtype=self.shards.dtype, device=self.dev)
@@ -136,13 +160,16 @@ class Zero3ParamManager:
             full.copy_(self.shard_view(b))
         elif self.custom:
             L = _lib.lib()
-            srcs = (ctypes.c_ulonglong * self.world)(*[self.shard_buf.ptrs[r] + b.state_off * esz
-                                                       for r in range(self.world)])
-            dsts = (ctypes.c_ulonglong * self.world)(*[full.data_ptr() + r * b.per * esz
-                                                       for r in range(self.world)])
-            sizes = (ctypes.c_ulonglong * self.world)(*[b.per * esz] * self.world)
-            with comm.comms_logger.record("all_gather(pull)", n * esz, self.world, full):
-                _lib.check(L.dtds_copy_segments(srcs, dsts, sizes, self.world, 0, _lib.stream_ptr()),
+            if skip is None or skip[1] <= b.lo or skip[0] >= b.hi:
+                segs = self._segments(b, b.lo, b.hi)
+            else:
+                segs = self._segments(b, b.lo, skip[0]) + self._segments(b, skip[1], b.hi)
+            ns = len(segs)
+            srcs = (ctypes.c_ulonglong * ns)(*[s for s, _, _ in segs])
+            dsts = (ctypes.c_ulonglong * ns)(*[full.data_ptr() + o for _, o, _ in segs])
+            sizes = (ctypes.c_ulonglong * ns)(*[nb for _, _, nb in segs])
+            with comm.comms_logger.record("all_gather(pull)", sum(nb for _, _, nb in segs), self.world, full):
+                _lib.check(L.dtds_copy_segments(srcs, dsts, sizes, ns, 0, _lib.stream_ptr()),
                            "dtds_copy_segments")
         else:
             comm.all_gather_into_tensor(full, self.shard_view(b).contiguous(), group=self.e.group)
@@ -155,12 +182,24 @@ class Zero3ParamManager:
                 blk.event = None
             return
         ctx = torch.cuda.stream(stream) if stream is not None else _Null()
+        lead = blk.lead
+        skip = (lead._flat_offset, lead._flat_offset + lead._numel) if lead is not None else None
         with ctx:
-            fulls = {b.index: self._gather_bucket(b) for b in blk.buckets}
+            fulls = {b.index: self._gather_bucket(b, skip) for b in blk.buckets}
         for p in blk.params:
             b = self.e._bucket_of[id(p)]
             o = p._flat_offset - b.lo
             p.data = fulls[b.index][o:o + p._numel].view(p._orig_shape)
+        if lead is not None:
+            # the consuming GEMM pulls this weight itself (see ops/functional.py: LinearFn)
+            if getattr(lead, "_ag_spec", None) is None:
+                from ..ops.kernels import GatherSpec
+                b = self.e._bucket_of[id(lead)]
+                esz = self.shards.element_size()
+                segs = [(s, nb) for s, _, nb in self._segments(b, skip[0], skip[1])]
+                row_bytes = lead._orig_shape[1] * esz
+                lead._ag_spec = GatherSpec(segs, lead._numel * esz, self.dev, chunk_rows=32, row_bytes=row_bytes)
+            lead._ag_pending = True
         if stream is not None:
             blk.event = torch.cuda.Event()
             blk.event.record(stream)
@@ -173,6 +212,8 @@ class Zero3ParamManager:
             return
         for p in blk.params:
             p.data = self._placeholder
+        if blk.lead is not None:
+            blk.lead._ag_pending = False
         blk.live = False
         blk.event = None
 
@@ -223,6 +264,21 @@ class Zero3ParamManager:
         """Materialises every parameter (checkpoint export / evaluation outside the engine)."""
         for blk in self.blocks + [self.pinned]:
             self._materialize(blk)
+            if blk.lead is not None and getattr(blk.lead, "_ag_pending", False):
+                self._complete_lead(blk.lead)
+
+    def _complete_lead(self, p) -> None:
+        """Plain gather of a weight that was left for a fused all-gather GEMM."""
+        b = self.e._bucket_of[id(p)]
+        segs = self._segments(b, p._flat_offset, p._flat_offset + p._numel)
+        ns = len(segs)
+        base = p.data.data_ptr() - (p._flat_offset - b.lo) * self.shards.element_size()
+        srcs = (ctypes.c_ulonglong * ns)(*[s for s, _, _ in segs])
+        dsts = (ctypes.c_ulonglong * ns)(*[base + o for _, o, _ in segs])
+        sizes = (ctypes.c_ulonglong * ns)(*[nb for _, _, nb in segs])
+        _lib.check(_lib.lib().dtds_copy_segments(srcs, dsts, sizes, ns, 0, _lib.stream_ptr()),
+                   "dtds_copy_segments")
+        p._ag_pending = False
 
 
 class _Null:

@@ -43,6 +43,20 @@ int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const void* bias,
                       int b_mn_major, int act, int out_fp32, int accumulate, float alpha,
                       int block_n, int max_ctas, const void* ready_flags, unsigned ready_epoch,
                       int rows_per_flag, cudaStream_t stream);
+/* ZeRO-3: parameter all-gather fused with the consuming GEMM (zero_dp_training.py --stage 3;
+ * DeepSpeed gathers with all_gather_into_tensor and then calls cuBLAS).  B_local is filled by
+ * fetch warps of the GEMM kernel from `nseg` source segments (peer-mapped shard addresses;
+ * segment i covers bytes [seg_begin[i], seg_begin[i+1]) of B) in chunks of `chunk_bytes` (whole
+ * rows); flags[chunk] is raised to `epoch` when a chunk has landed and the TMA producers wait on
+ * it, so transfer and tensor-core work overlap tile by tile.  b_mn_major = 1 is the dgrad form
+ * (dX = dY * W, flags indexed along K).  `epoch` must increase from call to call.              */
+int dtds_gemm_bf16_allgather(const void* A, void* B_local, void* D, const void* bias,
+                             const void* residual, int M, int N, int K, int lda, int ldb, int ldd,
+                             int ld_res, int b_mn_major, int act, int block_n,
+                             const unsigned long long* seg_src, const unsigned long long* seg_begin,
+                             int nseg, unsigned chunk_bytes, void* flags, unsigned epoch,
+                             cudaStream_t stream);
+
 /* Development aid: per-CTA clock64() timeline of the GEMM kernel into buf[grid][8]; NULL = off. */
 int dtds_gemm_set_debug_buffer(long long* buf);
 

@@ -224,6 +224,10 @@ def zero_stages_match_stage0(rank, world, arch="bloom-tiny"):
         sd = engine.consolidated_fp32_state_dict()
         results[stage] = torch.cat([v.flatten().float().cpu() for k, v in sorted(sd.items())])
         mem[stage] = engine.optimizer_state_bytes()
+        if stage == 3 and bf16 and world > 1:
+            from dtds_b200.ops import _lib
+            assert _lib.call_counts.get("dtds_gemm_bf16_allgather", 0) > 0, "fused all-gather GEMM was not used"
+            assert _lib.call_counts.get("dtds_zero_step", 0) > 0, "fused RS+Adam kernel was not used"
         if stage == 3:
             assert engine.param3.resident_parameter_bytes() * world <= \
                 sum(p._numel for p in engine.flat.params) * (2 if bf16 else 4) * 1.2 + 65536 * world
@@ -282,3 +286,42 @@ def pipeline_matches_single_process(rank, world, chunks=4):
             assert err < tol, f"module {idx} {n}: {err}"
     idle = bert.collect_idle_time()
     assert set(idle.keys()) == set(range(world))
+
+
+def allgather_gemm_matches_gathered(rank, world):
+    """The all-gather fused GEMM (weights pulled from peer shards by the kernel's fetch warps)
+    equals the GEMM on a weight that was gathered beforehand; forward and dgrad forms."""
+    from dtds_b200 import comm
+    from dtds_b200.ops import kernels as K
+    from dtds_b200.ops import reference as ref
+    dev = _dev(rank)
+    ctx = comm.symm_context()
+    for (M, N, Kd) in [(512, 3072, 1024), (512, 1024, 4096), (2048, 768, 768)]:
+        torch.manual_seed(3)
+        w_full = (torch.randn(N, Kd, device=dev) * 0.05).to(torch.bfloat16)   # same on all ranks
+        per = N * Kd // world
+        shard_buf = ctx.new_buffer(per * 2)
+        shard = shard_buf.tensor(torch.bfloat16, per)
+        shard.copy_(w_full.reshape(-1)[rank * per:(rank + 1) * per])
+        torch.cuda.synchronize(); dist.barrier()
+        torch.manual_seed(10 + rank)
+        x = torch.randn(M, Kd, device=dev).to(torch.bfloat16)
+        bias = torch.randn(N, device=dev).to(torch.bfloat16)
+        segs = [(shard_buf.ptrs[r], per * 2) for r in range(world)]
+        spec = K.GatherSpec(segs, N * Kd * 2, dev, chunk_rows=32, row_bytes=Kd * 2)
+        w_local = torch.zeros(N, Kd, dtype=torch.bfloat16, device=dev)
+        for rep in range(2):   # second call reuses flags with a higher epoch
+            w_local.zero_()
+            y = K.gemm_allgather(x, w_local, spec, bias=bias, act=ref.ACT_GELU_TANH)
+            torch.cuda.synchronize()
+            assert torch.equal(w_local, w_full), "kernel did not assemble the full weight"
+            want = K.gemm(x, w_full, bias=bias, act=ref.ACT_GELU_TANH)
+            assert torch.equal(y, want), (M, N, Kd, rep, (y.float() - want.float()).abs().max().item())
+        # dgrad form: dx = dy · W with W consumed MN-major, flags along K
+        dy = torch.randn(M, N, device=dev).to(torch.bfloat16)
+        w_local.zero_()
+        dx = K.gemm_allgather(dy, w_local, spec, b_mn_major=True)
+        torch.cuda.synchronize()
+        want = K.gemm(dy, w_full, b_mn_major=True)
+        assert torch.equal(dx, want), ("dgrad", M, N, Kd)
+        dist.barrier()

@@ -38,3 +38,7 @@ def test_zero_stages_match_stage0(arch):
 @pytest.mark.parametrize("chunks", [1, 4])
 def test_pipeline_matches_single_process(chunks):
     run_distributed("pipeline_matches_single_process", world=2, backend="nccl", args=(chunks,), timeout=600)
+
+
+def test_allgather_fused_gemm():
+    run_distributed("allgather_gemm_matches_gathered", world=2, backend="nccl")
