@@ -167,3 +167,50 @@ class SymmContext:
             self.all_reduce(sc, 0, padded, t.dtype, scale=scale, algo=2)
             t.view(torch.uint8).reshape(-1).copy_(stage[:nbytes])
         return t
+
+
+class McastBuffer:
+    """Symmetric buffer that is also bound to an NVSwitch multicast object (NVLS).
+
+    Allocation, handle exchange and the cuMulticast* binding come from
+    ``torch.distributed._symmetric_memory`` (cuMem + fabric/fd handles); the kernels that use the
+    resulting addresses are ours (csrc/comm_p2p.cu: allreduce_nvls_kernel).  ``available`` is False
+    when the platform gives no multicast address (no NVSwitch, driver without NVLS): callers then
+    stay on the P2P kernels."""
+
+    def __init__(self, nbytes: int, group=None):
+        import torch.distributed._symmetric_memory as tsm
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.nbytes = (int(nbytes) + 255) // 256 * 256
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self.available = False
+        self.mc_ptr = 0
+        try:
+            self._t = tsm.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+            pg = group if group is not None else dist.group.WORLD
+            self._hdl = tsm.rendezvous(self._t, pg)
+            self.mc_ptr = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+            self.ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+            self.local_ptr = self.ptrs[self.rank]
+            self.ptr_array = (ctypes.c_ulonglong * self.world)(*self.ptrs)
+            self.available = self.mc_ptr != 0
+        except Exception as e:  # noqa: BLE001
+            self.error = f"{type(e).__name__}: {e}"
+            self._t = None
+
+    def tensor(self, dtype: torch.dtype, numel: int | None = None, offset_bytes: int = 0) -> torch.Tensor:
+        esz = torch.empty((), dtype=dtype).element_size()
+        if numel is None:
+            numel = (self.nbytes - offset_bytes) // esz
+        return self._t[offset_bytes:offset_bytes + numel * esz].view(dtype)
+
+
+def all_reduce_nvls(ctx: "SymmContext", buf: McastBuffer, offset_bytes: int, nbytes: int, dtype, *,
+                    scale: float = 1.0, blocks: int = 0) -> None:
+    """In-place NVLS all-reduce of a range of a multicast-bound buffer."""
+    assert buf.available and dtype in (torch.bfloat16, torch.float32)
+    rc = _lib.lib().dtds_allreduce_nvls(buf.mc_ptr, ctx.signal.ptr_array, ctx.rank, ctx.world, offset_bytes,
+                                        nbytes, DTYPE_CODE[dtype], float(scale), int(blocks), _lib.stream_ptr())
+    _lib.check(rc, "dtds_allreduce_nvls")

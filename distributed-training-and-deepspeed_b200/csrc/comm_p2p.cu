@@ -638,3 +638,81 @@ extern "C" int dtds_copy_segments(const unsigned long long* src_ptrs,
   }
   return 0;
 }
+
+// ------------------------------------------------------------------------- NVLS (multimem)
+// Two-shot all-reduce through the NVSwitch multicast object: `mc` is the multicast address of the
+// symmetric buffer (every rank's copy bound to one multicast object).  multimem.ld_reduce makes
+// the switch read the vector from all ranks and return the sum (one request, 1/n of the P2P
+// inbound traffic); multimem.st writes the result into every rank's copy in one store.  Rank r
+// handles slice r.  Barriers are the same signal-pad barriers as the P2P kernels.
+namespace dtds {
+template <bool BF16>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_nvls_kernel(PeerTable pt, char* mc, size_t off_bytes, size_t nvec, float scale) {
+  cross_gpu_barrier(pt, 0);
+  const size_t per = (nvec + pt.world - 1) / pt.world;
+  const size_t v0 = per * pt.rank;
+  const size_t v1 = min(nvec, v0 + per);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  auto ld = [&](char* addr) -> uint4 {
+    uint4 r;
+    if (BF16)
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(addr) : "memory");
+    else
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(addr) : "memory");
+    return r;
+  };
+  auto st = [&](char* addr, uint4 r) {
+    if (scale != 1.f) {
+      if (BF16) {
+        uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) w[i] = pack_bf16x2(bf16_lo(w[i]) * scale, bf16_hi(w[i]) * scale);
+        r = make_uint4(w[0], w[1], w[2], w[3]);
+      } else {
+        r.x = __float_as_uint(__uint_as_float(r.x) * scale);
+        r.y = __float_as_uint(__uint_as_float(r.y) * scale);
+        r.z = __float_as_uint(__uint_as_float(r.z) * scale);
+        r.w = __float_as_uint(__uint_as_float(r.w) * scale);
+      }
+    }
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "r"(r.x),
+                 "r"(r.y), "r"(r.z), "r"(r.w)
+                 : "memory");
+  };
+  char* base = mc + off_bytes;
+  size_t v = v0 + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (; v + 3 * stride < v1; v += 4 * stride) {  // four switch reductions in flight per thread
+    const uint4 r0 = ld(base + v * 16);
+    const uint4 r1 = ld(base + (v + stride) * 16);
+    const uint4 r2 = ld(base + (v + 2 * stride) * 16);
+    const uint4 r3 = ld(base + (v + 3 * stride) * 16);
+    st(base + v * 16, r0);
+    st(base + (v + stride) * 16, r1);
+    st(base + (v + 2 * stride) * 16, r2);
+    st(base + (v + 3 * stride) * 16, r3);
+  }
+  for (; v < v1; v += stride) st(base + v * 16, ld(base + v * 16));
+  cross_gpu_barrier(pt, 1);
+}
+}  // namespace dtds
+
+// dtype: 0 bf16, 1 fp32.  `mc_ptr` = multicast address of the buffer (cuMulticast* binding, e.g.
+// obtained through torch.distributed._symmetric_memory), `signal_ptrs` = per-rank signal pads.
+extern "C" int dtds_allreduce_nvls(unsigned long long mc_ptr, const unsigned long long* signal_ptrs,
+                                   int rank, int world, size_t off_bytes, size_t nbytes, int dtype,
+                                   float scale, int blocks, cudaStream_t stream) {
+  if (nbytes == 0) return 0;
+  if ((nbytes % 16) || (off_bytes % 16) || mc_ptr == 0 || dtype < 0 || dtype > 1) return -2;
+  dtds::PeerTable pt;
+  if (dtds::fill_table(&pt, signal_ptrs, signal_ptrs, rank, world)) return -1;
+  const size_t nvec = nbytes / 16;
+  const int nb = dtds::comm_blocks((nvec + world - 1) / world, blocks > 0 ? blocks : 96);
+  char* mc = reinterpret_cast<char*>(mc_ptr);
+  if (dtype == 0) dtds::allreduce_nvls_kernel<true><<<nb, dtds::kCommThreads, 0, stream>>>(pt, mc, off_bytes, nvec, scale);
+  else dtds::allreduce_nvls_kernel<false><<<nb, dtds::kCommThreads, 0, stream>>>(pt, mc, off_bytes, nvec, scale);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -78,8 +78,12 @@ class DistributedDataParallel(nn.Module):
         self.device = p0.device
         if device_ids is not None and self.device.type == "cuda":
             assert self.device.index == torch.device("cuda", device_ids[0]).index
+        import os
+        nvls = os.environ.get("DTDS_NVLS", "auto").lower()
+        want_mc = nvls in ("1", "force", "on") or (nvls == "auto" and self.world >= 4)
         self.flat = FlatBuffers(params, grad_dtype=grad_dtype, symmetric=True, group=process_group,
-                                pad_total_to=64 * max(self.world, 1))
+                                pad_total_to=64 * max(self.world, 1), multicast_grads=want_mc)
+        self._nvls = getattr(self.flat.grad_buf, "mc_ptr", 0) != 0
         self._custom = self.flat.symmetric and comm.custom_kernels_active(self.flat.grad_flat)
         self._verify_replicas()
         if broadcast_parameters:
@@ -175,8 +179,14 @@ class DistributedDataParallel(nn.Module):
                 s = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
                 e = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
                 s.record()
-                ctx.all_reduce(self.flat.grad_buf, b.lo * esz, nbytes, g.dtype, scale=1.0 / self.world,
-                               algo=3, blocks=self.comm_blocks)
+                if self._nvls and nbytes >= (256 << 10) and g.dtype in (torch.bfloat16, torch.float32):
+                    # in-switch reduction: multimem.ld_reduce + multimem.st (csrc/comm_p2p.cu)
+                    from ..comm.symm import all_reduce_nvls
+                    all_reduce_nvls(ctx, self.flat.grad_buf, b.lo * esz, nbytes, g.dtype,
+                                    scale=1.0 / self.world, blocks=self.comm_blocks or 32)
+                else:
+                    ctx.all_reduce(self.flat.grad_buf, b.lo * esz, nbytes, g.dtype, scale=1.0 / self.world,
+                                   algo=3, blocks=self.comm_blocks)
                 e.record()
             comm.comms_logger.record_events("all_reduce", nbytes, self.world, s, e)
             self._events.append(e)

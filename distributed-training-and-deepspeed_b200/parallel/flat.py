@@ -28,7 +28,7 @@ class FlatBuffers:
     def __init__(self, params, *, param_dtype: torch.dtype | None = None,
                  grad_dtype: torch.dtype | None = None, device=None, align: int = 64,
                  pad_total_to: int = 64, symmetric: bool = False, group=None,
-                 with_grads: bool = True):
+                 with_grads: bool = True, multicast_grads: bool = False):
         self.params = unique_params(params)
         assert self.params, "no parameters"
         p0 = self.params[0]
@@ -54,8 +54,18 @@ class FlatBuffers:
             self.param_buf = ctx.new_buffer(self.total * esz_p)
             self.param_flat = self.param_buf.tensor(self.param_dtype, self.total)
             if with_grads:
-                self.grad_buf = ctx.new_buffer(self.total * esz_g)
+                self.grad_buf = None
+                if multicast_grads:  # NVLS: gradient buffer bound to an NVSwitch multicast object
+                    from ..comm.symm import McastBuffer
+                    mb = McastBuffer(self.total * esz_g, group)
+                    ok = torch.tensor([1 if mb.available else 0], device=self.device)
+                    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+                    if int(ok.item()) == 1:
+                        self.grad_buf = mb
+                if self.grad_buf is None:
+                    self.grad_buf = ctx.new_buffer(self.total * esz_g)
                 self.grad_flat = self.grad_buf.tensor(self.grad_dtype, self.total)
+                self.grad_flat.zero_()
         else:
             self.param_flat = torch.zeros(self.total, dtype=self.param_dtype, device=self.device)
             if with_grads:

@@ -148,6 +148,12 @@ int dtds_broadcast(const unsigned long long* data_ptrs, const unsigned long long
                    cudaStream_t stream);
 int dtds_device_barrier(const unsigned long long* signal_ptrs, int rank, int world,
                         cudaStream_t stream);
+/* NVLS two-shot all-reduce: multimem.ld_reduce (sum inside the NVSwitch) + multimem.st (one store
+ * lands in every rank's copy) on the multicast address `mc_ptr` of a symmetric buffer; in place.
+ * dtype 0 bf16 (fp32 accumulation), 1 fp32.                                                      */
+int dtds_allreduce_nvls(unsigned long long mc_ptr, const unsigned long long* signal_ptrs, int rank,
+                        int world, size_t off_bytes, size_t nbytes, int dtype, float scale,
+                        int blocks, cudaStream_t stream);
 /* ZeRO step in ONE kernel: reduce-scatter of bf16 gradients + Adam on the owned fp32 partition +
  * all-gather (push) of the updated bf16 parameters.  Offsets / sizes in elements, multiples of 8. */
 int dtds_zero_step(const unsigned long long* grad_ptrs, const unsigned long long* signal_ptrs,

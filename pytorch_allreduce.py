@@ -63,6 +63,10 @@ def sweep(rank, world_size, port, out_path, max_bytes):
     create_process_group(rank, world_size, "nccl", port)
     ctx = comm.symm_context()
     buf = ctx.new_buffer(max_bytes)
+    from dtds_b200.comm.symm import McastBuffer, all_reduce_nvls
+    mc = McastBuffer(max_bytes)
+    if rank == 0:
+        print("NVLS multicast buffer:", "available" if mc.available else f"unavailable ({getattr(mc, 'error', 'no multicast address')})")
     results = []
     size = 1024
     while size <= max_bytes:
@@ -76,14 +80,23 @@ def sweep(rank, world_size, port, out_path, max_bytes):
         if size <= (512 << 10):
             row["custom_oneshot_ms"] = _time_ms(lambda: ctx.all_reduce(buf, 0, size, torch.bfloat16, out=out, algo=1), iters, 5)
         row["custom_twoshot_ms"] = _time_ms(lambda: ctx.all_reduce(buf, 0, size, torch.bfloat16, algo=2), iters, 5)
+        if mc.available and size >= (1 << 16):
+            mt = mc.tensor(torch.bfloat16, n)
+            mt.fill_(1.0)
+            all_reduce_nvls(ctx, mc, 0, size, torch.bfloat16, scale=1.0 / world_size)
+            torch.cuda.synchronize()
+            assert torch.all(mt == 1.0), "NVLS all-reduce produced a wrong result"
+            row["custom_nvls_ms"] = _time_ms(lambda: all_reduce_nvls(ctx, mc, 0, size, torch.bfloat16), iters, 5)
         row["nccl_ms"] = _time_ms(lambda: dist.all_reduce(plain), iters, 5)
-        best = min(v for k, v in row.items() if k.startswith("custom"))
+        best = min(v for k, v in row.items() if k.startswith("custom") and k.endswith("_ms"))
         f = 2 * (world_size - 1) / world_size * size / 1e6   # bus bytes / 1e6: ms -> GB/s
         row["custom_busbw_GBps"] = f / best
         row["nccl_busbw_GBps"] = f / row["nccl_ms"]
         results.append(row)
         if rank == 0:
-            print(f"{size:>12d} B  custom {row['custom_busbw_GBps']:9.2f} GB/s ({best * 1e3:9.1f} us)   "
+            algo = min((v, k) for k, v in row.items() if k.startswith("custom") and k.endswith("_ms"))[1][7:-3]
+            row["custom_algo"] = algo
+            print(f"{size:>12d} B  custom[{algo:>7s}] {row['custom_busbw_GBps']:9.2f} GB/s ({best * 1e3:9.1f} us)   "
                   f"nccl {row['nccl_busbw_GBps']:9.2f} GB/s ({row['nccl_ms'] * 1e3:9.1f} us)", flush=True)
         size *= 4
     if rank == 0 and out_path:

@@ -42,3 +42,10 @@ def test_pipeline_matches_single_process(chunks):
 
 def test_allgather_fused_gemm():
     run_distributed("allgather_gemm_matches_gathered", world=2, backend="nccl")
+
+
+def test_ddp_nvls_gradient_allreduce(monkeypatch):
+    """Same DDP equivalence with the gradient buffer bound to an NVSwitch multicast object and the
+    buckets reduced by the multimem kernel (forced on: by default NVLS is used from 4 ranks up)."""
+    monkeypatch.setenv("DTDS_NVLS", "1")
+    run_distributed("ddp_matches_single_process", world=2, backend="nccl", args=(0.5,))
