@@ -304,6 +304,108 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
   for (int c = threadIdx.x; c < 2 * cols; c += blockDim.x) out[c] = sm[c];
 }
 
+// Row-parallel variant used when there are too few rows per warp for the register-accumulating
+// kernel above to pay off (the reference's 2048-token batches): pass A computes dz (and the
+// pre-dropout gradient) one warp per row with no cross-row state; pass B is a column reduction of
+// dy*xhat and dy over row slices (same access pattern as colsum) into `partial`.
+__global__ void __launch_bounds__(256)
+ln_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ z,
+                 const float* __restrict__ mean, const float* __restrict__ rstd,
+                 const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ dz_extra,
+                 __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ dx_drop, int rows, int cols,
+                 float p_drop, uint64_t seed, const uint64_t* __restrict__ seed_dev) {
+  if (seed_dev != nullptr) seed += *seed_dev * 0xD1B54A32D192ED03ull;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const DropRng rng = make_drop_rng(seed, p_drop);
+  const int nvec = cols >> 3;
+  const size_t base = static_cast<size_t>(row) * cols;
+  const float mu = mean[row], rs = rstd[row];
+  float s1 = 0.f, s2 = 0.f;
+  for (int vi = lane; vi < nvec; vi += 32) {
+    const uint4 d = *reinterpret_cast<const uint4*>(dy + base + vi * 8);
+    const uint4 zz = *reinterpret_cast<const uint4*>(z + base + vi * 8);
+    const uint4 g = *reinterpret_cast<const uint4*>(gamma + vi * 8);
+    const uint32_t dw[4] = {d.x, d.y, d.z, d.w}, zw[4] = {zz.x, zz.y, zz.z, zz.w}, gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const float gd0 = bf16_lo(dw[t]) * bf16_lo(gw[t]), gd1 = bf16_hi(dw[t]) * bf16_hi(gw[t]);
+      s1 += gd0 + gd1;
+      s2 += gd0 * ((bf16_lo(zw[t]) - mu) * rs) + gd1 * ((bf16_hi(zw[t]) - mu) * rs);
+    }
+  }
+  s1 = warp_sum(s1) / cols;
+  s2 = warp_sum(s2) / cols;
+  for (int vi = lane; vi < nvec; vi += 32) {
+    const uint4 d = *reinterpret_cast<const uint4*>(dy + base + vi * 8);
+    const uint4 zz = *reinterpret_cast<const uint4*>(z + base + vi * 8);
+    const uint4 g = *reinterpret_cast<const uint4*>(gamma + vi * 8);
+    const uint32_t dw[4] = {d.x, d.y, d.z, d.w}, zw[4] = {zz.x, zz.y, zz.z, zz.w}, gw[4] = {g.x, g.y, g.z, g.w};
+    float o[8];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const float xh0 = (bf16_lo(zw[t]) - mu) * rs, xh1 = (bf16_hi(zw[t]) - mu) * rs;
+      o[2 * t] = rs * (bf16_lo(dw[t]) * bf16_lo(gw[t]) - s1 - xh0 * s2);
+      o[2 * t + 1] = rs * (bf16_hi(dw[t]) * bf16_hi(gw[t]) - s1 - xh1 * s2);
+    }
+    if (dz_extra != nullptr) {
+      const uint4 e = *reinterpret_cast<const uint4*>(dz_extra + base + vi * 8);
+      const uint32_t ew[4] = {e.x, e.y, e.z, e.w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) { o[2 * t] += bf16_lo(ew[t]); o[2 * t + 1] += bf16_hi(ew[t]); }
+    }
+    *reinterpret_cast<uint4*>(dz + base + vi * 8) =
+        make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+    if (dx_drop != nullptr) {
+      float ks[8];
+      drop_scale8(rng, base + vi * 8, ks);
+#pragma unroll
+      for (int t = 0; t < 8; ++t) o[t] *= ks[t];
+      *reinterpret_cast<uint4*>(dx_drop + base + vi * 8) =
+          make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+    }
+  }
+}
+// grid = (cols / 64 tiles, row splits); partial[split][0..cols) = sum dy*xhat, [cols..2cols) = sum dy.
+__global__ void __launch_bounds__(256)
+ln_bwd_dgb_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ z,
+                  const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ partial,
+                  int rows, int cols) {
+  __shared__ float sg[8][64], sb[8][64];
+  const int c0 = blockIdx.x * 64;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = c0 + tx * 2;
+  const int rows_per = (rows + gridDim.y - 1) / gridDim.y;
+  const int r_begin = blockIdx.y * rows_per, r_end = min(rows, r_begin + rows_per);
+  float g0 = 0.f, g1 = 0.f, b0 = 0.f, b1 = 0.f;
+  if (c + 1 < cols + 1 && c < cols) {
+#pragma unroll 4
+    for (int r = r_begin + ty; r < r_end; r += 8) {
+      const uint32_t d = *reinterpret_cast<const uint32_t*>(dy + static_cast<size_t>(r) * cols + c);
+      const uint32_t zz = *reinterpret_cast<const uint32_t*>(z + static_cast<size_t>(r) * cols + c);
+      const float mu = mean[r], rs = rstd[r];
+      const float d0 = bf16_lo(d), d1 = bf16_hi(d);
+      g0 += d0 * ((bf16_lo(zz) - mu) * rs);
+      g1 += d1 * ((bf16_hi(zz) - mu) * rs);
+      b0 += d0;
+      b1 += d1;
+    }
+  }
+  sg[ty][tx * 2] = g0; sg[ty][tx * 2 + 1] = g1;
+  sb[ty][tx * 2] = b0; sb[ty][tx * 2 + 1] = b1;
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    const int j = threadIdx.x & 63;
+    const bool is_b = threadIdx.x >= 64;
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += is_b ? sb[k][j] : sg[k][j];
+    if (c0 + j < cols)
+      partial[static_cast<size_t>(blockIdx.y) * 2 * cols + (is_b ? cols : 0) + c0 + j] = t;
+  }
+}
+
 // Reduces [nblocks, 2, cols] partials into dgamma/dbeta (bf16 or fp32, optionally accumulating).
 // Block = 32 columns x 8 segments of the partial rows; coalesced loads, smem tree at the end.
 __global__ void __launch_bounds__(256)
@@ -570,6 +672,10 @@ extern "C" int dtds_layernorm_fwd(const void* x, const void* residual, const voi
 
 extern "C" int dtds_layernorm_bwd_blocks(int rows, int cols) {
   (void)cols;
+  if (rows <= 64 * dtds::sm_count() && cols % 2 == 0) {  // row-parallel path: `blocks` = row splits
+    int splits = (rows + 127) / 128;
+    return splits < 1 ? 1 : (splits > 64 ? 64 : splits);
+  }
   int blocks = (rows + 31) / 32;  // >= 4 rows per warp so the register accumulators pay off
   const int cap = dtds::sm_count();
   return blocks < cap ? (blocks < 1 ? 1 : blocks) : cap;
@@ -585,6 +691,25 @@ extern "C" int dtds_layernorm_bwd(const void* dy, const void* z, const float* me
   if (rows <= 0) return 0;
   if (cols % 8 != 0) return -1;
   const int blocks = dtds_layernorm_bwd_blocks(rows, cols);
+  if (rows <= 64 * dtds::sm_count() && cols % 2 == 0) {
+    ln_bwd_dx_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(
+        static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(z), mean, rstd,
+        static_cast<const __nv_bfloat16*>(gamma), static_cast<const __nv_bfloat16*>(dz_extra),
+        static_cast<__nv_bfloat16*>(dz), static_cast<__nv_bfloat16*>(dx_drop), rows, cols, p_drop, seed,
+        reinterpret_cast<const uint64_t*>(seed_dev));
+    DTDS_HOST_CHECK(cudaGetLastError());
+    if (dgamma != nullptr && dbeta != nullptr) {
+      dim3 grid((cols + 63) / 64, blocks);
+      ln_bwd_dgb_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(dy),
+                                                  static_cast<const __nv_bfloat16*>(z), mean, rstd, partial,
+                                                  rows, cols);
+      DTDS_HOST_CHECK(cudaGetLastError());
+      ln_bwd_finalize_kernel<<<(2 * cols + 31) / 32, 256, 0, stream>>>(partial, blocks, cols, dgamma, dbeta,
+                                                                       grads_fp32, accumulate);
+      DTDS_HOST_CHECK(cudaGetLastError());
+    }
+    return 0;
+  }
   const size_t smem = sizeof(float) * 2 * cols;
 #define DTDS_LN_BWD(VPL_)                                                                        \
   ln_bwd_kernel<VPL_><<<blocks, 256, smem, stream>>>(                                             \

@@ -81,6 +81,9 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
     assert out.stride(-1) == 1 and out.shape == (M, N)
     out_fp32 = out.dtype == torch.float32
     L = _lib.lib()
+    if block_n == 0 and ready_flags is None:
+        block_n = _tuned_block_n(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn_major,
+                                 b_mn_major, act, out_fp32, alpha)
     rc = L.dtds_gemm_bf16_ex(
         a.data_ptr(), b.data_ptr(), out.data_ptr(), _lib.ptr(bias), _lib.ptr(residual),
         _lib.ptr(pre_out), _lib.ptr(dact_in), M, N, K, a.stride(0), b.stride(0), out.stride(0),
@@ -91,6 +94,59 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
         _lib.stream_ptr())
     _lib.check(rc, "dtds_gemm_bf16_ex")
     return out
+
+
+_tune_cache: dict = {}
+_AUTOTUNE = __import__("os").environ.get("DTDS_AUTOTUNE", "1") != "0"
+
+
+def _tuned_block_n(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn, b_mn, act, out_fp32, alpha):
+    """Measured tile-width choice.  At the token counts of the reference's scripts the GEMMs have
+    one or two waves of tiles and are bound by L2 fill rate, launch latency and epilogue cost in
+    proportions that differ per shape, so the first eager call of every distinct problem times the
+    three BLOCK_N variants (CUDA events, scratch outputs) and caches the winner.  Never runs while a
+    CUDA graph is being captured (the warm-up steps before capture populate the cache); 0 = let the
+    C++ cost model decide."""
+    if not _AUTOTUNE:
+        return 0
+    key = (M, N, K, a_mn, b_mn, int(act), bias is not None, residual is not None, pre_out is not None,
+           dact_in is not None, out_fp32, a.stride(0), b.stride(0), out.stride(0))
+    hit = _tune_cache.get(key)
+    if hit is not None:
+        return hit
+    if torch.cuda.is_current_stream_capturing():
+        return 0
+    cands = [bn for bn in (64, 128, 256) if bn == 64 or N > bn // 2]
+    if len(cands) == 1:
+        _tune_cache[key] = cands[0]
+        return cands[0]
+    tmp = torch.empty_strided(out.shape, out.stride(), dtype=out.dtype, device=out.device)
+    tmp_pre = torch.empty_strided(pre_out.shape, pre_out.stride(), dtype=pre_out.dtype, device=out.device) \
+        if pre_out is not None else None
+    stream = _lib.stream_ptr()
+
+    def run(bn):
+        return L.dtds_gemm_bf16_ex(
+            a.data_ptr(), b.data_ptr(), tmp.data_ptr(), _lib.ptr(bias), _lib.ptr(residual), _lib.ptr(tmp_pre),
+            _lib.ptr(dact_in), M, N, K, a.stride(0), b.stride(0), tmp.stride(0),
+            residual.stride(0) if residual is not None else 0, dact_in.stride(0) if dact_in is not None else 0,
+            int(a_mn), int(b_mn), int(act), int(out_fp32), 0, float(alpha), bn, 0, None, 0, 0, stream)
+
+    best, best_t = 0, float("inf")
+    for bn in cands:
+        if run(bn) != 0:
+            continue
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(4):
+            run(bn)
+        e1.record()
+        e1.synchronize()
+        t = e0.elapsed_time(e1)
+        if t < best_t:
+            best, best_t = bn, t
+    _tune_cache[key] = best
+    return best
 
 
 # ---------------------------------------------------------------------------------- LayerNorm

@@ -63,7 +63,14 @@ def run(rank, device_count, args, backend):
     last = (not distributed) or rank == device_count - 1
     training_start_time = time.time()
     progress_bar = tqdm(range(args.training_steps)) if (not args.verbose and last) else None
-    for batch in train_dataloader:
+    steady_start, steady_from = None, min(3, max(args.training_steps - 1, 0))
+    for step_idx, batch in enumerate(train_dataloader):
+        if step_idx == steady_from:   # connection set-up, autotuning and allocator growth are over
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
+            steady_start = time.time()
+            for tr in bert.trackers.values():
+                tr.reset()
         if distributed:
             bert.forward_backward(batch["input_ids"], batch["labels"])
         else:
@@ -82,9 +89,14 @@ def run(rank, device_count, args, backend):
     if torch.cuda.is_available():
         torch.cuda.synchronize()
     training_end_time = time.time()
-    table = summarize_idle_time(bert, args.training_steps)
+    steady_steps = max(args.training_steps - steady_from, 1)
+    table = summarize_idle_time(bert, steady_steps)
     if last:
         print(f"\nTotal Training Time: {training_end_time - training_start_time:.2f} seconds")
+        if steady_start is not None:
+            dt = training_end_time - steady_start
+            print(f"Steady state (steps {steady_from + 1}..{args.training_steps}): {dt / steady_steps * 1e3:.2f} ms/step, "
+                  f"{args.batch_size * steady_steps / dt:.1f} samples/s; idle times below exclude the first {steady_from} steps")
         print("\nAverage Idle Time per Device:")
         print(table)
     if distributed:

@@ -81,7 +81,12 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
 
     training_start_time = time.time()
     progress_bar = tqdm(range(training_steps)) if rank == 0 and not quiet else None
-    for batch in train_dataloader:
+    steady_start, steady_from = None, 3
+    for step_idx, batch in enumerate(train_dataloader):
+        if step_idx == steady_from:
+            if on_gpu:
+                torch.cuda.synchronize()
+            steady_start = time.time()
         input_ids = batch["input_ids"].to(device)
         labels = batch["labels"].to(device)
         loss = model_engine(input_ids, labels=labels).loss
@@ -97,6 +102,11 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
     training_end_time = time.time()
     if rank == 0:
         print(f"\nTotal Training Time: {training_end_time - training_start_time:.2f} seconds")
+        n_local = len(train_dataloader)
+        if steady_start is not None and n_local > steady_from:
+            dt = (training_end_time - steady_start) / (n_local - steady_from)
+            print(f"Steady state (local steps {steady_from + 1}..{n_local}): {dt * 1e3:.2f} ms/step, "
+                  f"{batch_size * world_size / dt:.1f} samples/s over {world_size} rank(s)")
 
     total_comms_latency = comm.comms_logger.total_latency_ms()
     comm.log_summary()
