@@ -298,15 +298,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         char* dst = p.fetch_dst + lo;
         const unsigned long long nv = (hi - lo) >> 4;
         unsigned long long v = ft;
-        for (; v + 3 * kFetchThreads < nv; v += 4 * kFetchThreads) {
-          const uint4 x0 = ld_sys_v4(src + (v << 4));
-          const uint4 x1 = ld_sys_v4(src + ((v + kFetchThreads) << 4));
-          const uint4 x2 = ld_sys_v4(src + ((v + 2 * kFetchThreads) << 4));
-          const uint4 x3 = ld_sys_v4(src + ((v + 3 * kFetchThreads) << 4));
-          *reinterpret_cast<uint4*>(dst + (v << 4)) = x0;
-          *reinterpret_cast<uint4*>(dst + ((v + kFetchThreads) << 4)) = x1;
-          *reinterpret_cast<uint4*>(dst + ((v + 2 * kFetchThreads) << 4)) = x2;
-          *reinterpret_cast<uint4*>(dst + ((v + 3 * kFetchThreads) << 4)) = x3;
+        // 8 independent 128-bit peer loads in flight per thread: 128 threads x 8 x 16 B = 16 KiB per
+        // CTA, ~2.4 MB chip-wide, which covers the ~2.5 us NVLink round trip at full link rate.
+        for (; v + 7 * kFetchThreads < nv; v += 8 * kFetchThreads) {
+          uint4 x[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) x[u] = ld_sys_v4(src + ((v + u * kFetchThreads) << 4));
+#pragma unroll
+          for (int u = 0; u < 8; ++u) *reinterpret_cast<uint4*>(dst + ((v + u * kFetchThreads) << 4)) = x[u];
         }
         for (; v < nv; v += kFetchThreads)
           *reinterpret_cast<uint4*>(dst + (v << 4)) = ld_sys_v4(src + (v << 4));

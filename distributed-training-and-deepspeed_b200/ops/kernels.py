@@ -492,6 +492,10 @@ class GatherSpec:
 
     def __init__(self, segments, total_bytes, device, chunk_rows, row_bytes):
         import ctypes
+        # enough chunks that every SM's fetch warps have work (>= ~2 per SM), at least 8 rows each
+        n_rows = total_bytes // row_bytes
+        while chunk_rows > 8 and n_rows // chunk_rows < 2 * 148:
+            chunk_rows //= 2
         assert 1 <= len(segments) <= 16, "at most 16 source segments"
         assert sum(n for _, n in segments) == total_bytes
         self.nseg = len(segments)

@@ -64,7 +64,7 @@ def collectives_match_torch(rank, world):
     assert torch.all(t == world - 1 + 7), "broadcast"
     # stress: many back-to-back in-place all-reduces reuse the signal pads without host syncs
     g = buf.tensor(torch.bfloat16, 1 << 16)
-    for it in range(200):
+    for it in range(10000):
         g.fill_(1.0)
         ctx.all_reduce(buf, 0, (1 << 16) * 2, torch.bfloat16, scale=1.0 / world)
     torch.cuda.synchronize()
