@@ -1,0 +1,41 @@
+"""The reference's entry points, run end to end on CPU (gloo, world_size 2) with tiny shapes:
+BASELINE.json config 1 (`model/transformer.py` block through `data_parallel_training.py`), the
+ZeRO script under the in-repo launcher, the model-parallel script in pipeline mode."""
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(args, timeout=600, env=None):
+    e = dict(os.environ)
+    e.update(env or {})
+    e["CUDA_VISIBLE_DEVICES"] = e.get("CUDA_VISIBLE_DEVICES", "")
+    return subprocess.run([sys.executable, *args], cwd=ROOT, capture_output=True, text=True, timeout=timeout, env=e)
+
+
+def test_ddp_script_transformer_block_gloo_world2():
+    r = _run(["data_parallel_training.py", "--backend", "gloo", "--device-count", "2", "--model", "block",
+              "--batch-size", "2", "--training-steps", "8", "--seq-len", "64", "--port", "12421"])
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.stdout.count("Total Training Time:") == 2   # every rank prints it, like the reference
+
+
+def test_zero_script_under_launcher_gloo_world2():
+    for stage in (2, 3):
+        r = _run(["-m", "dtds_b200.launch", "--nproc-per-node", "2", "zero_dp_training.py", "--stage", str(stage),
+                  "--model_name", "bloom-tiny", "--training-steps", "6", "--seq-len", "64", "--quiet"])
+        out = r.stdout + r.stderr
+        assert r.returncode == 0, out[-3000:]
+        assert f"ZeRO Stage: {stage}" in out and "Optimizer: lr=0.00015; betas=(0.9, 0.999); eps=1e-08" in out
+        assert "Total Training Time:" in out and "Total Communication Latency:" in out
+        assert "Comm. Op" in out   # the summary table
+
+
+def test_model_parallel_script_pipeline_gloo_world2():
+    r = _run(["model_parallel_training.py", "--backend", "gloo", "--device-count", "2", "--model", "tiny",
+              "--batch-size", "8", "--training-steps", "3", "--seq-len", "64", "--pipeline", "--port", "12423"])
+    out = r.stdout + r.stderr
+    assert r.returncode == 0, out[-3000:]
+    assert "Total Training Time:" in out and "Average Idle Time (ms)" in out
