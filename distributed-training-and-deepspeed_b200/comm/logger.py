@@ -71,6 +71,9 @@ class CommsLogger:
             yield
             return
         on_gpu = tensor is not None and tensor.is_cuda
+        if on_gpu and torch.cuda.is_current_stream_capturing():
+            yield   # timing events cannot be resolved from inside a CUDA graph; replays are not logged
+            return
         if on_gpu:
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s.record()

@@ -37,7 +37,8 @@ def resolve_config(model_name):
     return get_config(model_name)
 
 
-def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_len=512, quiet=False):
+def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_len=512, quiet=False,
+          cuda_graph=False):
     from dtds_b200 import comm
     from dtds_b200.models import build_model
     from dtds_b200.parallel import zero
@@ -81,6 +82,14 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
 
     training_start_time = time.time()
     progress_bar = tqdm(range(training_steps)) if rank == 0 and not quiet else None
+    def step_fn(input_ids, labels):
+        loss = model_engine(input_ids, labels=labels).loss
+        model_engine.backward(loss)
+        model_engine.step()
+        return loss
+
+    graphed = None
+    use_graph = cuda_graph and on_gpu and stage < 3   # stage 3 re-points parameter storage per block
     steady_start, steady_from = None, 3
     for step_idx, batch in enumerate(train_dataloader):
         if step_idx == steady_from:
@@ -89,9 +98,13 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
             steady_start = time.time()
         input_ids = batch["input_ids"].to(device)
         labels = batch["labels"].to(device)
-        loss = model_engine(input_ids, labels=labels).loss
-        model_engine.backward(loss)
-        model_engine.step()
+        if use_graph and input_ids.shape[0] == batch_size:
+            if graphed is None:   # capture forward + backward + fused ZeRO step kernels once
+                from dtds_b200.parallel.graph import GraphedStep
+                graphed = GraphedStep(step_fn, [input_ids, labels], warmup=2)
+            loss = graphed(input_ids, labels)
+        else:
+            loss = step_fn(input_ids, labels)
         if rank == 0:
             if not quiet:
                 memory_status("Memory stats after training step:")
@@ -126,6 +139,7 @@ if __name__ == "__main__":
     parser.add_argument("--seq-len", type=int, default=512)
     parser.add_argument("--fp32", action="store_true", help="keep fp32 parameters (library collectives)")
     parser.add_argument("--quiet", action="store_true", help="no per-step MEMSTATS / progress bar")
+    parser.add_argument("--cuda-graph", action="store_true", help="replay the step as one CUDA graph (stages 0-2)")
     args, extra_args = parser.parse_known_args()
     train(args.model_name, args.batch_size, args.training_steps, args.stage, *extra_args,
-          bf16=False if args.fp32 else None, seq_len=args.seq_len, quiet=args.quiet)
+          bf16=False if args.fp32 else None, seq_len=args.seq_len, quiet=args.quiet, cuda_graph=args.cuda_graph)
