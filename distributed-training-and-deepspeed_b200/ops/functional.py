@@ -55,6 +55,67 @@ def grad_done(param) -> None:
             cb(param)
 
 
+# ------------------------------------------------------------------ weight-gradient side stream
+# dgrad feeds the next layer's backward, wgrad feeds nobody until the optimizer (or the bucket
+# collective).  At the reference's batch sizes one GEMM has 50-300 tiles for 148 SMs, so running
+# the wgrad (+ bias column sum) of a layer on a second stream lets it fill the SMs the dgrad chain
+# leaves idle.  The side stream is joined back at the end of backward (autograd engine callback);
+# gradient-ready callbacks fire inside the side-stream context, so the engines' events are
+# recorded on the stream that actually produced the gradient.
+_WGRAD_SIDE = __import__("os").environ.get("DTDS_WGRAD_STREAM", "1") != "0"
+_side_streams: dict = {}
+_join_queued: dict = {}
+
+
+class _OnSideStream:
+    def __init__(self, *tensors, params=()):
+        self.tensors = [t for t in tensors if t is not None and t.is_cuda]
+        # gradients written from several places (tied embeddings) stay on the main stream so the
+        # overwrite-then-accumulate order of their producers is the program order
+        shared = any(p is not None and getattr(p, "_grad_uses", 1) > 1 for p in params)
+        self.active = _WGRAD_SIDE and bool(self.tensors) and not shared
+
+    def __enter__(self):
+        if not self.active:
+            return self
+        dev = self.tensors[0].device
+        side = _side_streams.get(dev)
+        if side is None:
+            side = _side_streams[dev] = torch.cuda.Stream(dev)
+        cur = torch.cuda.current_stream(dev)
+        side.wait_stream(cur)
+        for t in self.tensors:
+            t.record_stream(side)
+        if not _join_queued.get(dev, False):
+            _join_queued[dev] = True
+
+            def join(dev=dev, side=side):
+                torch.cuda.current_stream(dev).wait_stream(side)
+                _join_queued[dev] = False
+            try:
+                torch.autograd.Variable._execution_engine.queue_callback(join)
+            except RuntimeError:   # not inside a backward pass: join right away on exit
+                _join_queued[dev] = False
+                self._join_now = (dev, side)
+        self._ctx = torch.cuda.stream(side)
+        self._ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if not self.active:
+            return False
+        self._ctx.__exit__(*exc)
+        if getattr(self, "_join_now", None):
+            dev, side = self._join_now
+            torch.cuda.current_stream(dev).wait_stream(side)
+        return False
+
+
+def wgrad_side_stream(device):
+    """The side stream weight gradients of `device` are produced on (None if never used)."""
+    return _side_streams.get(device)
+
+
 def _emit(param, compute):
     """compute(out, accumulate) -> tensor.  Returns the value autograd should see for `param`."""
     if param is None or not param.requires_grad:
@@ -128,8 +189,9 @@ class LinearFn(torch.autograd.Function):
                 weight._ag_pending = False
             else:
                 dx = K.gemm(du, weight, b_mn_major=True).view(ctx.in_shape)
-        dw = _wgrad(du, x2, weight) if ctx.needs_input_grad[1] else None
-        db = _bgrad(du, bias) if (bias is not None and ctx.needs_input_grad[2]) else None
+        with _OnSideStream(du, x2, params=(weight, bias)):
+            dw = _wgrad(du, x2, weight) if ctx.needs_input_grad[1] else None
+            db = _bgrad(du, bias) if (bias is not None and ctx.needs_input_grad[2]) else None
         return dx, dw, db, None, dres
 
 
@@ -164,12 +226,14 @@ class MLPFn(torch.autograd.Function):
         if not df2.is_contiguous():
             df2 = df2.contiguous()
         dres = df if ctx.has_res else None
+        with _OnSideStream(df2, a, params=(w2, b2)):
+            dw2 = _wgrad(df2, a, w2)
+            db2 = _bgrad(df2, b2) if b2 is not None else None
         du = K.gemm(df2, w2, b_mn_major=True, act=ctx.act, dact_in=u)
-        dw2 = _wgrad(df2, a, w2)
-        db2 = _bgrad(df2, b2) if b2 is not None else None
         dx = K.gemm(du, w1, b_mn_major=True).view(ctx.in_shape) if ctx.needs_input_grad[0] else None
-        dw1 = _wgrad(du, x2, w1)
-        db1 = _bgrad(du, b1) if b1 is not None else None
+        with _OnSideStream(du, x2, params=(w1, b1)):
+            dw1 = _wgrad(du, x2, w1)
+            db1 = _bgrad(du, b1) if b1 is not None else None
         return dx, dw1, db1, dw2, db2, None, dres
 
 
@@ -378,8 +442,9 @@ class LMHeadLossFn(torch.autograd.Function):
         x2, weight, bias = ctx.saved_tensors
         d, ctx.d = ctx.d, None
         dx = K.gemm(d, weight, b_mn_major=True).view(ctx.in_shape) if ctx.needs_input_grad[0] else None
-        dw = _wgrad(d, x2, weight)
-        db = _bgrad(d, bias) if bias is not None else None
+        with _OnSideStream(d, x2, params=(weight, bias)):
+            dw = _wgrad(d, x2, weight)
+            db = _bgrad(d, bias) if bias is not None else None
         return dx, dw, db, None, None, None, None, None
 
 

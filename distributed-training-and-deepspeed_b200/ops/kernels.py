@@ -225,7 +225,7 @@ def colsum(x, out=None, accumulate=False):
     if out is None:
         out = torch.empty(cols, dtype=x.dtype, device=x.device)
         accumulate = False
-    scratch = _scratch_f32(x.device, cols + cols // 64 + 130, "colsum")  # sums + counters, left zeroed
+    scratch = _scratch_f32(x.device, cols + cols // 64 + 130, f"colsum@{_lib.stream_ptr()}")  # per stream; left zeroed
     rc = _lib.lib().dtds_colsum(x.data_ptr(), rows, cols, x.stride(0), scratch.data_ptr(),
                                 out.data_ptr(), int(out.dtype == torch.float32), int(accumulate),
                                 _lib.stream_ptr())

@@ -174,6 +174,7 @@ class DistributedDataParallel(nn.Module):
             ready = torch.cuda.Event()
             ready.record(cur)
             self._comm_stream.wait_event(ready)
+            self._wait_wgrad_stream(self._comm_stream, cur)
             ctx = comm.symm_context(self.group)
             with torch.cuda.stream(self._comm_stream):
                 s = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
@@ -194,8 +195,19 @@ class DistributedDataParallel(nn.Module):
             view = g[b.lo:b.hi]
             comm.all_reduce(view, group=self.group, backend="nccl", scale=1.0 / self.world)
 
+    def _wait_wgrad_stream(self, waiter, cur):
+        """Gradients of one bucket may come from the main stream and from the weight-gradient side
+        stream (ops/functional.py); the collective must be ordered after both."""
+        from ..ops.functional import wgrad_side_stream
+        side = wgrad_side_stream(self.device)
+        if side is not None and side != cur:
+            waiter.wait_stream(side)
+
     def _finalize_backward(self):
         """End of backward: launch stragglers, join the comm stream, expose gradients."""
+        if self.device.type == "cuda":
+            cur = torch.cuda.current_stream(self.device)
+            self._wait_wgrad_stream(cur, cur)
         if self._require_sync:
             for b in self.buckets:
                 if not b.launched:  # parameters that got no gradient this step

@@ -254,10 +254,14 @@ class ZeroEngine(nn.Module):
         if self._custom and self.world > 1:
             cur = torch.cuda.current_stream(self.device)
             stream = self._comm_stream if overlap else cur
+            from ..ops.functional import wgrad_side_stream
+            side = wgrad_side_stream(self.device)
             if overlap:
                 ready = torch.cuda.Event()
                 ready.record(cur)
                 stream.wait_event(ready)
+            if side is not None and side != stream:
+                stream.wait_stream(side)   # gradients of this bucket produced on the wgrad stream
             ctx = comm.symm_context(self.group)
             timing = comm.comms_logger.enabled and not torch.cuda.is_current_stream_capturing()
             with torch.cuda.stream(stream):
