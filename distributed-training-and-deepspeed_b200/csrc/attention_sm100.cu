@@ -670,11 +670,30 @@ extern "C" int dtds_attention_fwd(const void* qkv, int ld_qkv, void* out, float*
   return 0;
 }
 
+extern "C" int dtds_attention_bwd_parts(const void* qkv, int ld_qkv, const void* out, const void* dout,
+                                        const float* lse, float* delta, void* dqkv, const float* key_bias,
+                                        const float* alibi_slopes, int B, int S, int heads, int head_dim,
+                                        float scale, int causal, float p_drop, unsigned long long seed,
+                                        const unsigned long long* seed_dev, int parts, cudaStream_t stream);
+
 extern "C" int dtds_attention_bwd(const void* qkv, int ld_qkv, const void* out, const void* dout,
                                   const float* lse, float* delta, void* dqkv, const float* key_bias,
                                   const float* alibi_slopes, int B, int S, int heads, int head_dim,
                                   float scale, int causal, float p_drop, unsigned long long seed,
                                   const unsigned long long* seed_dev, cudaStream_t stream) {
+  return dtds_attention_bwd_parts(qkv, ld_qkv, out, dout, lse, delta, dqkv, key_bias, alibi_slopes, B, S,
+                                  heads, head_dim, scale, causal, p_drop, seed, seed_dev, 7, stream);
+}
+
+// `parts` selects what to launch: 1 = delta (rowsum(dO*O)), 2 = dK/dV kernel, 4 = dQ kernel.  The
+// dK/dV and dQ kernels only depend on delta and write disjoint columns of dqkv, so a caller may
+// put them on two streams (each occupies a whole SM per CTA with 192 CTAs for 148 SMs: run
+// together they share 2.6 waves instead of 2 + 2).
+extern "C" int dtds_attention_bwd_parts(const void* qkv, int ld_qkv, const void* out, const void* dout,
+                                        const float* lse, float* delta, void* dqkv, const float* key_bias,
+                                        const float* alibi_slopes, int B, int S, int heads, int head_dim,
+                                        float scale, int causal, float p_drop, unsigned long long seed,
+                                        const unsigned long long* seed_dev, int parts, cudaStream_t stream) {
   if (check_attn_args(B, S, heads, head_dim, ld_qkv)) return -1;
   const int H = heads * 64;
   CUtensorMap tm, tmdo;
@@ -692,13 +711,19 @@ extern "C" int dtds_attention_bwd(const void* qkv, int ld_qkv, const void* out, 
     DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDkdvSmem));
     attr_set = true;
   }
-  attn_delta_kernel<<<(B * S + 7) / 8, 256, 0, stream>>>(
-      static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, B, S, heads);
-  DTDS_HOST_CHECK(cudaGetLastError());
+  if (parts & 1) {
+    attn_delta_kernel<<<(B * S + 7) / 8, 256, 0, stream>>>(
+        static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, B, S, heads);
+    DTDS_HOST_CHECK(cudaGetLastError());
+  }
   dim3 grid(S / 128, B * heads);
-  attn_bwd_dkdv_kernel<<<grid, kAttnThreads, kDkdvSmem, stream>>>(tm, tmdo, p);
-  DTDS_HOST_CHECK(cudaGetLastError());
-  attn_bwd_dq_kernel<<<grid, kAttnThreads, kDqSmem, stream>>>(tm, tmdo, p);
-  DTDS_HOST_CHECK(cudaGetLastError());
+  if (parts & 2) {
+    attn_bwd_dkdv_kernel<<<grid, kAttnThreads, kDkdvSmem, stream>>>(tm, tmdo, p);
+    DTDS_HOST_CHECK(cudaGetLastError());
+  }
+  if (parts & 4) {
+    attn_bwd_dq_kernel<<<grid, kAttnThreads, kDqSmem, stream>>>(tm, tmdo, p);
+    DTDS_HOST_CHECK(cudaGetLastError());
+  }
   return 0;
 }

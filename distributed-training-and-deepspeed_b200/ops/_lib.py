@@ -107,7 +107,7 @@ def ptr(t) -> int | None:
 
 # kernels launched per C call (default 1); used for the launch accounting bench.py reports
 _KERNELS_PER_CALL = {"dtds_cross_entropy": 2, "dtds_layernorm_bwd": 3,
-                     "dtds_attention_bwd": 3, "dtds_adam_flat": 2}
+                     "dtds_attention_bwd": 1, "dtds_adam_flat": 2}
 
 
 call_counts: dict = {}  # C entry point name -> number of calls (tests assert on fused paths)

@@ -425,6 +425,10 @@ def cast(src, dst):
 
 
 # --------------------------------------------------------------------------------- attention
+_ATTN_TWO_STREAMS = __import__("os").environ.get("DTDS_ATTN_TWO_STREAMS", "1") != "0"
+_attn_streams: dict = {}
+
+
 def _split_qkv(qkv, B, S, heads):
     H = qkv.shape[1] // 3
     d = H // heads
@@ -474,11 +478,32 @@ def attention_bwd(qkv, out, dout, lse, B, S, heads, *, scale, causal=False, key_
     dout = _c(dout)
     dqkv = torch.empty(B * S, 3 * H, dtype=qkv.dtype, device=qkv.device)
     delta = torch.empty(B, heads, S, dtype=torch.float32, device=qkv.device)
-    rc = _lib.lib().dtds_attention_bwd(
-        qkv.data_ptr(), qkv.stride(0), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
-        delta.data_ptr(), dqkv.data_ptr(), _lib.ptr(key_bias), _lib.ptr(alibi), B, S, heads, d,
-        float(scale), int(causal), float(p_drop), int(seed), _seed_ptr(), _lib.stream_ptr())
-    _lib.check(rc, "dtds_attention_bwd")
+    L = _lib.lib()
+
+    def launch(parts):
+        rc = L.dtds_attention_bwd_parts(
+            qkv.data_ptr(), qkv.stride(0), out.data_ptr(), dout.data_ptr(), lse.data_ptr(),
+            delta.data_ptr(), dqkv.data_ptr(), _lib.ptr(key_bias), _lib.ptr(alibi), B, S, heads, d,
+            float(scale), int(causal), float(p_drop), int(seed), _seed_ptr(), parts, _lib.stream_ptr())
+        _lib.check(rc, "dtds_attention_bwd")
+
+    if not _ATTN_TWO_STREAMS:
+        launch(7)
+        return dqkv
+    # delta on the main stream, then the dQ kernel on a side stream concurrently with dK/dV
+    dev = qkv.device
+    side = _attn_streams.get(dev)
+    if side is None:
+        side = _attn_streams[dev] = torch.cuda.Stream(dev)
+    cur = torch.cuda.current_stream(dev)
+    launch(1)
+    side.wait_stream(cur)
+    with torch.cuda.stream(side):
+        launch(4)
+    launch(2)
+    cur.wait_stream(side)
+    for t in (qkv, out, dout, lse, delta, dqkv):
+        t.record_stream(side)
     return dqkv
 
 

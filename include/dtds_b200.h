@@ -116,6 +116,13 @@ int dtds_attention_bwd(const void* qkv, int ld_qkv, const void* out, const void*
                        const float* alibi_slopes, int B, int S, int heads, int head_dim,
                        float scale, int causal, float p_drop, unsigned long long seed,
                        const unsigned long long* seed_dev, cudaStream_t stream);
+/* Same, launching only the selected parts: 1 = delta, 2 = dK/dV kernel, 4 = dQ kernel (the last two
+ * are independent given delta and may run on different streams).                                */
+int dtds_attention_bwd_parts(const void* qkv, int ld_qkv, const void* out, const void* dout,
+                             const float* lse, float* delta, void* dqkv, const float* key_bias,
+                             const float* alibi_slopes, int B, int S, int heads, int head_dim,
+                             float scale, int causal, float p_drop, unsigned long long seed,
+                             const unsigned long long* seed_dev, int parts, cudaStream_t stream);
 
 /* ---- Symmetric-memory runtime + in-kernel collectives over NVLink peer memory (replaces
  *      ProcessGroupNCCL/NCCL behind pytorch_allreduce.py:31, the DDP Reducer all-reduce behind
