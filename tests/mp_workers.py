@@ -325,3 +325,49 @@ def allgather_gemm_matches_gathered(rank, world):
         want = K.gemm(dy, w_full, b_mn_major=True)
         assert torch.equal(dx, want), ("dgrad", M, N, Kd)
         dist.barrier()
+
+
+def zero_checkpoint_resume(rank, world, stage=2):
+    """Save at step 2, rebuild the engine from scratch, load, continue: same parameters as the
+    uninterrupted run; the consolidated model file has the module's parameter names."""
+    import os
+    import tempfile
+    from dtds_b200.models import build_model, get_config
+    from dtds_b200.parallel import zero
+    from dtds_b200.utils.ckpt import load_checkpoint, save_checkpoint
+    dev = _dev(rank)
+    bf16 = dev.type == "cuda"
+    cfg = get_config("opt-tiny").replace(hidden_dropout_prob=0.0)
+    ids = torch.randint(0, cfg.vocab_size, (2, 128), generator=torch.Generator().manual_seed(21 + rank))
+
+    def make():
+        torch.manual_seed(0)
+        model = build_model(cfg)
+        eng, opt, _, _ = zero.initialize(model=model, model_parameters=model.parameters(), config=_ds_config(stage, bf16))
+        return eng, opt
+
+    def steps(eng, n):
+        for _ in range(n):
+            loss = eng(ids.to(dev), labels=ids.to(dev)).loss
+            eng.backward(loss)
+            eng.step()
+
+    e1, _ = make()
+    steps(e1, 4)
+    want = e1.consolidated_fp32_state_dict()
+    e2, o2 = make()
+    steps(e2, 2)
+    path = [tempfile.mkdtemp(prefix="dtds_ckpt_") if rank == 0 else None]
+    dist.broadcast_object_list(path, src=0)
+    save_checkpoint(path[0], e2, o2, step=2)
+    e3, o3 = make()
+    assert load_checkpoint(path[0], e3, o3) == 2
+    steps(e3, 2)
+    got = e3.consolidated_fp32_state_dict()
+    assert set(got) == set(want)
+    for k in want:
+        assert torch.allclose(got[k].float().cpu(), want[k].float().cpu(), atol=1e-6 if not bf16 else 2e-2), k
+    if rank == 0:
+        sd = torch.load(os.path.join(path[0], "model.pt"))
+        names = {n for n, _ in e3.module.named_parameters()}
+        assert names <= set(sd.keys())

@@ -21,3 +21,8 @@ def test_zero_stages_match_stage0_gloo():
 
 def test_gpipe_matches_single_process_gloo():
     run_distributed("pipeline_matches_single_process", world=2, backend="gloo", args=(4,), timeout=600)
+
+
+def test_zero_checkpoint_resume_gloo():
+    run_distributed("zero_checkpoint_resume", world=2, backend="gloo", args=(2,), timeout=600)
+    run_distributed("zero_checkpoint_resume", world=2, backend="gloo", args=(3,), timeout=600)
