@@ -41,6 +41,9 @@ def parse_args():
     ap.add_argument("--seq-len", type=int, default=512)
     ap.add_argument("--bucket-size", type=int, default=25)
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--no-overlap-optimizer", action="store_true",
+                    help="one Adam launch after backward instead of per-bucket updates under backward")
+    ap.add_argument("--adam-bucket-mb", type=float, default=32.0)
     ap.add_argument("--comm", default=None, choices=[None, "custom", "nccl"])
     return ap.parse_args()
 
@@ -239,7 +242,12 @@ def build_ours(args, cfg, dev, world, ids_h, labels_h):
     model = build_model(cfg).to(device=dev, dtype=torch.bfloat16)
     model.train()
     net = DistributedDataParallel(model, device_ids=[dev.index], bucket_cap_mb=args.bucket_size) if world > 1 else model
-    opt = HFAdamW(model.parameters(), lr=5e-5)
+    # Adam runs per bucket under backward (after the bucket's all-reduce when world > 1)
+    overlap = not args.no_overlap_optimizer
+    opt = HFAdamW(model.parameters(), lr=5e-5, overlap_with_backward=overlap and world == 1,
+                  overlap_bucket_mb=args.adam_bucket_mb)
+    if overlap and world > 1:
+        net.fuse_optimizer(opt)
 
     def train_step(ids, labels):
         opt.zero_grad()

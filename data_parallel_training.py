@@ -57,7 +57,8 @@ class _BlockRegressor(torch.nn.Module):
         return SimpleNamespace(loss=loss, logits=logits)
 
 
-def train(rank, world_size, batch_size, training_steps, bucket_size, model, backend, port, use_graph, seq_len):
+def train(rank, world_size, batch_size, training_steps, bucket_size, model, backend, port, use_graph, seq_len,
+          overlap_optimizer=False):
     from dtds_b200.models import build_model, get_config
     from dtds_b200.optim import HFAdamW
     from dtds_b200.parallel.ddp import DistributedDataParallel
@@ -85,6 +86,8 @@ def train(rank, world_size, batch_size, training_steps, bucket_size, model, back
 
     ddp = DistributedDataParallel(net, device_ids=[rank] if on_gpu else None, bucket_cap_mb=bucket_size)
     ddp.train()
+    if overlap_optimizer:
+        ddp.fuse_optimizer(optimizer)   # Adam per bucket right behind its all-reduce, under backward
 
     def step_fn(input_ids, labels):
         optimizer.zero_grad()
@@ -126,6 +129,7 @@ if __name__ == "__main__":
     parser.add_argument("--port", type=int, default=12355)
     parser.add_argument("--seq-len", type=int, default=None)
     parser.add_argument("--cuda-graph", action="store_true")
+    parser.add_argument("--overlap-optimizer", action="store_true")
     args = parser.parse_args()
 
     backend = args.backend or ("nccl" if torch.cuda.is_available() else "gloo")
@@ -133,5 +137,5 @@ if __name__ == "__main__":
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     mp.spawn(train,
              args=(device_count, args.batch_size, args.training_steps, args.bucket_size, args.model, backend,
-                   args.port, args.cuda_graph, args.seq_len),
+                   args.port, args.cuda_graph, args.seq_len, args.overlap_optimizer),
              nprocs=device_count, join=True)

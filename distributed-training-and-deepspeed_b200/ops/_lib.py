@@ -113,9 +113,9 @@ _KERNELS_PER_CALL = {"dtds_cross_entropy": 2, "dtds_layernorm_bwd": 3,
 call_counts: dict = {}  # C entry point name -> number of calls (tests assert on fused paths)
 
 
-def check(rc: int, what: str) -> None:
+def check(rc: int, what: str, kernels: int | None = None) -> None:
     global _launches
-    _launches += _KERNELS_PER_CALL.get(what, 1)
+    _launches += _KERNELS_PER_CALL.get(what, 1) if kernels is None else kernels
     call_counts[what] = call_counts.get(what, 0) + 1
     if rc != 0:
         raise NativeLibraryError(f"{what} failed with code {rc} (see stderr for details)")

@@ -45,6 +45,16 @@ def grad_target(param):
     return mg, bool(getattr(param, "_grad_written", False))
 
 
+def mark_shared_grad(param, uses: int) -> None:
+    """Declares that `uses` backward producers write this parameter's gradient (tied embeddings).
+    Models call it at the top of forward, not only in __init__: ``copy.deepcopy`` of a Parameter
+    drops Python attributes, and a lost mark would fire the gradient-ready callback (bucket
+    all-reduce / Adam) after the first producer."""
+    if getattr(param, "_grad_uses", 1) != uses:
+        param._grad_uses = uses
+        param._uses_pending = uses
+
+
 def grad_done(param) -> None:
     param._grad_written = True
     pending = getattr(param, "_uses_pending", 1) - 1
@@ -226,10 +236,11 @@ class MLPFn(torch.autograd.Function):
         if not df2.is_contiguous():
             df2 = df2.contiguous()
         dres = df if ctx.has_res else None
+        du = K.gemm(df2, w2, b_mn_major=True, act=ctx.act, dact_in=u)
+        # after the dgrad that reads w2: a gradient-ready callback may update w2 right away
         with _OnSideStream(df2, a, params=(w2, b2)):
             dw2 = _wgrad(df2, a, w2)
             db2 = _bgrad(df2, b2) if b2 is not None else None
-        du = K.gemm(df2, w2, b_mn_major=True, act=ctx.act, dact_in=u)
         dx = K.gemm(du, w1, b_mn_major=True).view(ctx.in_shape) if ctx.needs_input_grad[0] else None
         with _OnSideStream(du, x2, params=(w1, b1)):
             dw1 = _wgrad(du, x2, w1)

@@ -395,6 +395,10 @@ def adam_flat(p, g, m, v, step, *, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_
     `step` is an int32 device tensor holding the number of steps already taken."""
     if not _lib.use_native(p):
         t = int(step.item()) + 1
+        if p.numel() == 0:
+            if inc_step:
+                step += 1
+            return
         ref.adam_step(p, g, m, v, t, lr=lr, beta1=beta1, beta2=beta2, eps=eps,
                       weight_decay=weight_decay, adamw_mode=adamw_mode,
                       bias_correction=bias_correction, grad_scale=grad_scale)
@@ -410,7 +414,8 @@ def adam_flat(p, g, m, v, step, *, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_
         step.data_ptr(), int(inc_step), int(g.dtype == torch.float32), float(lr), float(beta1),
         float(beta2), float(eps), float(weight_decay), float(grad_scale), int(adamw_mode),
         int(bias_correction), _lib.stream_ptr())
-    _lib.check(rc, "dtds_adam_flat")
+    # launch accounting: the update kernel (if n > 0) and the step-count kernel (if inc_step)
+    _lib.check(rc, "dtds_adam_flat", kernels=int(p.numel() > 0) + int(bool(inc_step)))
 
 
 def cast(src, dst):

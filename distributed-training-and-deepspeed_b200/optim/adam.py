@@ -40,7 +40,8 @@ class FusedAdam(torch.optim.Optimizer):
     weight_decay).  ``adam_w_mode=True`` (default) is decoupled weight decay."""
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0,
-                 adam_w_mode=True, bias_correction=True, grad_dtype=None):
+                 adam_w_mode=True, bias_correction=True, grad_dtype=None, overlap_with_backward=False,
+                 overlap_bucket_mb: float = 32.0):
         params = list(params)
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
                         bias_correction=bias_correction)
@@ -61,17 +62,146 @@ class FusedAdam(torch.optim.Optimizer):
             self._flats.append(FlatBuffers(ps, grad_dtype=grad_dtype, device=dev))
         for f in self._flats:
             self._groups.append(_FlatGroup(f))
+        # ---- optional: update each bucket as soon as its gradients are final, under backward
+        self.overlap = bool(overlap_with_backward)
+        self._done: dict = {}      # id(group) -> list of (lo, hi) ranges already updated this step
+        self._obuckets = []        # (group, lo, hi, params)
+        self._opt_streams: dict = {}
+        self._overlap_bucket_mb = overlap_bucket_mb
+        if self.overlap:
+            self._build_overlap_buckets(overlap_bucket_mb)
+
+    # ------------------------------------------------------------------ overlapped update
+    def _build_overlap_buckets(self, bucket_mb: float) -> None:
+        """Own buckets (used when no DDP engine drives the optimizer): reverse parameter order,
+        `bucket_mb` MiB of parameters each, whole parameters only."""
+        for grp in self._groups:
+            f = grp.flat
+            cap = int(bucket_mb * (1 << 20)) // f.param_flat.element_size()
+            cur, cur_n = [], 0
+            groups = []
+            for i in reversed(range(len(f.params))):
+                n = f.params[i].numel()
+                if cur and cur_n + n > cap:
+                    groups.append(cur)
+                    cur, cur_n = [], 0
+                cur.append(i)
+                cur_n += n
+            if cur:
+                groups.append(cur)
+            hi = f.total
+            for idxs in groups:
+                lo = min(f.offsets[i] for i in idxs)
+                ps = [f.params[i] for i in idxs]
+                b = {"group": grp, "lo": lo, "hi": hi, "params": ps, "pending": len(ps)}
+                self._obuckets.append(b)
+                hi = lo
+                for p in ps:
+                    p._adam_bucket = b
+                    if getattr(p, "_on_grad_ready", None) is None:   # a DDP/ZeRO engine takes precedence
+                        p._on_grad_ready = self._param_ready
+
+    def _rebind(self) -> None:
+        """An engine wrapped the model after this optimizer was built (the reference scripts create
+        the optimizer first, data_parallel_training.py:34-44) and moved the parameters into its own
+        flat buffers: follow them, carrying master weights, moments and step count over."""
+        if not any(getattr(g.flat, "_superseded_by", None) is not None for g in self._groups):
+            return
+        new_groups = []
+        for grp in self._groups:
+            old = grp.flat
+            new = getattr(old, "_superseded_by", None)
+            if new is None:
+                new_groups.append(grp)
+                continue
+            moved = [p for p in old.params if getattr(p, "_flat_owner", None) is new]
+            stay = [p for p in old.params if getattr(p, "_flat_owner", None) is old and p.requires_grad]
+            if stay or (grp.lo, grp.hi) != (0, old.total):
+                raise RuntimeError("FusedAdam: only part of the parameters moved to another flat buffer; "
+                                   "build the optimizer after wrapping the model")
+            ng = _FlatGroup(new)
+            for p in moved:
+                o_old, o_new, n = old.offsets[_index_of(old.params, p)], p._flat_offset, p._numel
+                ng.exp_avg[o_new:o_new + n].copy_(grp.exp_avg[o_old:o_old + n])
+                ng.exp_avg_sq[o_new:o_new + n].copy_(grp.exp_avg_sq[o_old:o_old + n])
+                if ng.lowp and grp.lowp:
+                    ng.master[o_new:o_new + n].copy_(grp.master[o_old:o_old + n])
+            ng.step.copy_(grp.step)
+            new_groups.append(ng)
+            old._superseded_by = None
+        self._groups = new_groups
+        self._flats = [g.flat for g in new_groups]
+        self._done.clear()
+        if self.overlap:
+            self._obuckets = []
+            self._build_overlap_buckets(self._overlap_bucket_mb)
+
+    def _param_ready(self, p) -> None:
+        b = p._adam_bucket
+        b["pending"] -= 1
+        if b["pending"] == 0:
+            self.step_range(b["group"], b["lo"], b["hi"])
+
+    def _group_of(self, flat) -> "_FlatGroup":
+        for g in self._groups:
+            if g.flat is flat:
+                return g
+        raise KeyError("flat buffer not managed by this optimizer")
+
+    @torch.no_grad()
+    def step_range(self, group, lo: int, hi: int, stream=None) -> None:
+        """Adam on flat elements [lo, hi) now (gradients of that range are final).  Runs on
+        `stream` if given (a DDP engine passes its communication stream so the update follows the
+        bucket's all-reduce), else on the optimizer's side stream ordered after the current stream
+        and the weight-gradient stream.  ``step()`` skips ranges done here."""
+        self._rebind()
+        if not isinstance(group, _FlatGroup):
+            group = self._group_of(group)
+        f = group.flat
+        dev = f.param_flat.device
+        g0 = self.param_groups[0]
+        lr, (b1, b2), eps, wd = g0["lr"], g0["betas"], g0["eps"], g0["weight_decay"]
+
+        def run():
+            K.adam_flat(group.master[lo - group.lo:hi - group.lo], f.grad_flat[lo:hi],
+                        group.exp_avg[lo - group.lo:hi - group.lo], group.exp_avg_sq[lo - group.lo:hi - group.lo],
+                        group.step, lr=lr, beta1=b1, beta2=b2, eps=eps, weight_decay=wd,
+                        adamw_mode=self.adam_w_mode, bias_correction=g0.get("bias_correction", True),
+                        p_lp=f.param_flat[lo:hi] if group.lowp else None, inc_step=False)
+
+        if dev.type != "cuda":
+            run()
+        elif stream is not None:
+            with torch.cuda.stream(stream):
+                run()
+            self._opt_streams[dev] = stream
+        else:
+            from ..ops.functional import wgrad_side_stream
+            side = self._opt_streams.get(dev)
+            if side is None:
+                side = self._opt_streams[dev] = torch.cuda.Stream(dev)
+            cur = torch.cuda.current_stream(dev)
+            side.wait_stream(cur)
+            ws = wgrad_side_stream(dev)
+            if ws is not None:
+                side.wait_stream(ws)
+            with torch.cuda.stream(side):
+                run()
+        self._done.setdefault(id(group), []).append((lo, hi))
 
     @property
     def flats(self):
+        self._rebind()
         return self._flats
 
     def master_weights(self):
+        self._rebind()
         return [g.master for g in self._groups]
 
     @torch.no_grad()
     def step(self, closure=None):
         loss = closure() if closure is not None else None
+        self._rebind()
         g0 = self.param_groups[0]
         lr, (b1, b2), eps, wd = g0["lr"], g0["betas"], g0["eps"], g0["weight_decay"]
         for grp in self._groups:
@@ -79,28 +209,48 @@ class FusedAdam(torch.optim.Optimizer):
             f.absorb_autograd_grads()
             f.zero_unwritten_grads()
             dev = f.param_flat.device
+            done = sorted(self._done.pop(id(grp), []))
+            if dev.type == "cuda" and dev in self._opt_streams and done:
+                torch.cuda.current_stream(dev).wait_stream(self._opt_streams[dev])
+            # ranges not updated under backward (all of them unless overlap is on)
+            todo, pos = [], grp.lo
+            for lo, hi in done:
+                if lo > pos:
+                    todo.append((pos, lo))
+                pos = max(pos, hi)
+            if pos < grp.hi:
+                todo.append((pos, grp.hi))
             ctx = torch.cuda.device(dev) if dev.type == "cuda" else _null()
             with ctx:
-                K.adam_flat(grp.master, f.grad_flat[grp.lo:grp.hi], grp.exp_avg, grp.exp_avg_sq, grp.step,
-                            lr=lr, beta1=b1, beta2=b2, eps=eps, weight_decay=wd,
-                            adamw_mode=self.adam_w_mode, bias_correction=g0.get("bias_correction", True),
-                            p_lp=f.param_flat[grp.lo:grp.hi] if grp.lowp else None)
+                for lo, hi in todo:
+                    K.adam_flat(grp.master[lo - grp.lo:hi - grp.lo], f.grad_flat[lo:hi],
+                                grp.exp_avg[lo - grp.lo:hi - grp.lo], grp.exp_avg_sq[lo - grp.lo:hi - grp.lo],
+                                grp.step, lr=lr, beta1=b1, beta2=b2, eps=eps, weight_decay=wd,
+                                adamw_mode=self.adam_w_mode, bias_correction=g0.get("bias_correction", True),
+                                p_lp=f.param_flat[lo:hi] if grp.lowp else None, inc_step=False)
+                K.adam_flat(grp.master[:0], f.grad_flat[:0], grp.exp_avg[:0], grp.exp_avg_sq[:0], grp.step,
+                            lr=lr, inc_step=True)   # advances the device-side step count only
         return loss
 
     def zero_grad(self, set_to_none: bool = True):
+        self._rebind()
         for f in self._flats:
             f.reset_grad_state()
             for p in f.params:
                 p.grad = None
+        for b in self._obuckets:
+            b["pending"] = len(b["params"])
 
     # state_dict in torch format: per-flat fp32 master + moments + step
     def state_dict(self):
+        self._rebind()
         return {"param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups],
                 "flat_state": [{"master": g.master.detach().clone(), "exp_avg": g.exp_avg.clone(),
                                 "exp_avg_sq": g.exp_avg_sq.clone(), "step": g.step.clone(),
                                 "lo": g.lo, "hi": g.hi} for g in self._groups]}
 
     def load_state_dict(self, sd):
+        self._rebind()
         for g, s in zip(self.param_groups, sd["param_groups"]):
             g.update(s)
         for grp, s in zip(self._groups, sd["flat_state"]):
@@ -110,6 +260,13 @@ class FusedAdam(torch.optim.Optimizer):
             grp.step.copy_(s["step"])
             if grp.lowp:
                 grp.flat.param_flat[grp.lo:grp.hi].copy_(grp.master)
+
+
+def _index_of(params, p) -> int:
+    for i, q in enumerate(params):
+        if q is p:
+            return i
+    raise ValueError("parameter not in flat buffer")
 
 
 class _null:

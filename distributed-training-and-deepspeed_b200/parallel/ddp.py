@@ -101,6 +101,7 @@ class DistributedDataParallel(nn.Module):
             self.buckets.append(b)
             for p in b.params:
                 self._bucket_of[id(p)] = b
+        self.optimizer = None   # set by fuse_optimizer(): Adam per bucket right after its all-reduce
         self._require_sync = True
         self._accumulating = False
         self.expose_grads = True
@@ -162,12 +163,24 @@ class DistributedDataParallel(nn.Module):
         if b.pending == 0 and not b.launched:
             self._launch_bucket(b)
 
+    def fuse_optimizer(self, optimizer) -> None:
+        """Lets the engine run `optimizer.step_range` for a bucket on the communication stream as
+        soon as that bucket's all-reduce has been enqueued: the (HBM-bound) Adam update overlaps the
+        rest of backward instead of running after it (unpack fused with Adam).
+        ``optimizer.step()`` afterwards only advances the step count."""
+        self.optimizer = optimizer
+
+    def _step_bucket(self, b, stream):
+        if self.optimizer is not None and not self._accumulating:
+            self.optimizer.step_range(self.flat, b.lo, min(b.hi, self.flat.total), stream=stream)
+
     def _launch_bucket(self, b: _Bucket):
         b.launched = True
         g = self.flat.grad_flat
         esz = g.element_size()
         nbytes = (b.hi - b.lo) * esz
         if self.world < 2:
+            self._step_bucket(b, None)
             return
         if self._custom:
             cur = torch.cuda.current_stream(self.device)
@@ -190,10 +203,15 @@ class DistributedDataParallel(nn.Module):
                                    algo=3, blocks=self.comm_blocks)
                 e.record()
             comm.comms_logger.record_events("all_reduce", nbytes, self.world, s, e)
+            self._step_bucket(b, self._comm_stream)
+            if self.optimizer is not None:
+                e = torch.cuda.Event()
+                e.record(self._comm_stream)
             self._events.append(e)
         else:
             view = g[b.lo:b.hi]
             comm.all_reduce(view, group=self.group, backend="nccl", scale=1.0 / self.world)
+            self._step_bucket(b, None)
 
     def _wait_wgrad_stream(self, waiter, cur):
         """Gradients of one bucket may come from the main stream and from the weight-gradient side

@@ -79,6 +79,9 @@ class FlatBuffers:
                 p.data = view
                 if with_grads:
                     p.main_grad = self.grad_flat[o:o + p.numel()].view(p.shape)
+                prev = getattr(p, "_flat_owner", None)
+                if prev is not None and prev is not self:
+                    prev._superseded_by = self   # optimizers built on `prev` rebind (optim/adam.py)
                 p._flat_owner = self
                 p._orig_shape = tuple(p.shape)
                 p._numel = p.numel()

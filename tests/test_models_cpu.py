@@ -95,3 +95,51 @@ def test_causal_lm_shift_and_tied_head():
     ref = torch.nn.functional.cross_entropy(out.logits[:, :-1].reshape(-1, cfg.vocab_size), ids[:, 1:].reshape(-1))
     assert abs(out.loss.item() - ref.item()) < 1e-4
     assert m.head_weight is m.word_embeddings
+
+
+def _train_three_steps(overlap=False, ddp=False, opt_first=False, bucket_mb=0.05, deep=False):
+    """Three AdamW steps on bert-tiny (eval mode: no dropout noise); returns the flat weights."""
+    from dtds_b200.optim import HFAdamW
+    from dtds_b200.parallel.ddp import DistributedDataParallel as DDP
+    torch.manual_seed(0)
+    m = build_model(get_config("bert-tiny"))
+    if deep:   # deepcopy drops Python attributes of Parameters (the tied-embedding mark)
+        import copy
+        m = copy.deepcopy(m)
+    m.eval()
+    opt = None
+    if opt_first:   # the reference builds the optimizer before wrapping (data_parallel_training.py:34-44)
+        opt = HFAdamW(m.parameters(), lr=1e-3)
+    net = DDP(m, bucket_cap_mb=bucket_mb) if ddp else m
+    if opt is None:
+        opt = HFAdamW(m.parameters(), lr=1e-3, overlap_with_backward=overlap and not ddp,
+                      overlap_bucket_mb=bucket_mb)
+    if ddp and overlap:
+        net.fuse_optimizer(opt)
+    g = torch.Generator().manual_seed(1)
+    for _ in range(3):
+        ids = torch.randint(0, m.cfg.vocab_size, (2, 128), generator=g)
+        opt.zero_grad()
+        net(input_ids=ids, labels=ids).loss.backward()
+        opt.step()
+    return torch.cat([p.detach().flatten() for p in m.parameters()]), opt
+
+
+def test_adam_overlapped_with_backward_is_exact():
+    """Per-bucket Adam fired from the gradient-ready callbacks (own buckets, or the DDP engine's)
+    gives bit-identical weights to one update after backward."""
+    base, _ = _train_three_steps()
+    own, opt = _train_three_steps(overlap=True)
+    assert len(opt._obuckets) > 5
+    assert torch.equal(base, own)
+    fused, _ = _train_three_steps(overlap=True, ddp=True)
+    assert torch.equal(base, fused)
+    copied, _ = _train_three_steps(overlap=True, deep=True)
+    assert torch.equal(base, copied)
+
+
+def test_optimizer_built_before_ddp_wrap_follows_parameters():
+    base, _ = _train_three_steps()
+    late, opt = _train_three_steps(ddp=True, opt_first=True)
+    assert torch.equal(base, late)
+    assert getattr(opt.flats[0], "_superseded_by", None) is None
