@@ -48,21 +48,39 @@ struct AttnParams {
   __nv_bfloat16* dqkv;  // bwd: [B*S, 3H]
 };
 
-// Dropout keep-scales for 32 consecutive keys [jk0, jk0+32) of query row iq (jk0 even).
+// Compile-time specialisation of the score/softmax loops.  MODE < 0: every feature is a run-time
+// test (any combination works); MODE >= 0: bit 0 causal, bit 1 ALiBi, bit 2 dropout, bit 3 key
+// padding bias are constants and the untaken paths vanish from the 32-element inner loops (which
+// are issue-bound: ~25 -> ~12 instructions per score for the BERT case).
+template <int MODE>
+struct AttnFlags {
+  bool causal, alibi, drop, kbias;
+  __device__ __forceinline__ AttnFlags(const AttnParams& p, const DropRng& rng)
+      : causal(MODE < 0 ? p.causal != 0 : (MODE & 1) != 0),
+        alibi(MODE < 0 ? p.alibi != nullptr : (MODE & 2) != 0),
+        drop(MODE < 0 ? rng.thr != 0u : (MODE & 4) != 0),
+        kbias(MODE < 0 ? p.key_bias != nullptr : (MODE & 8) != 0) {}
+};
+
+__device__ __forceinline__ float ex2_approx(float x) {  // 2^x, one MUFU; -inf -> 0, denormals flushed
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// Dropout keep-scales for 32 consecutive keys [jk0, jk0+32) of query row iq (jk0 % 32 == 0, so
+// the 16 hash pairs share the high word of the pair index: one key derivation per chunk).
 __device__ __forceinline__ void attn_keep32(const DropRng& rng, const AttnParams& p, int bh, int iq,
                                             int jk0, float (&ks)[32]) {
   const uint64_t pair0 = ((static_cast<uint64_t>(bh) * p.S + iq) * p.S + jk0) >> 1;
+  const uint32_t key = drop_key(rng, static_cast<uint32_t>(pair0 >> 32));
+  const uint32_t lo0 = static_cast<uint32_t>(pair0);
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    const uint32_t b = drop_bits(rng, pair0 + k);
+    const uint32_t b = drop_bits_keyed(key, lo0 + k);
     ks[2 * k] = (b & 0xFFFFu) >= rng.thr ? rng.inv_keep : 0.f;
     ks[2 * k + 1] = (b >> 16) >= rng.thr ? rng.inv_keep : 0.f;
   }
-}
-// Single element (used where consecutive elements are not consecutive keys: the transposed kernel).
-__device__ __forceinline__ float attn_keep1(const DropRng& rng, const AttnParams& p, int bh, int iq,
-                                            int jk) {
-  return drop_scale1(rng, (static_cast<uint64_t>(bh) * p.S + iq) * p.S + jk);
 }
 __device__ __forceinline__ DropRng attn_rng(const AttnParams& p) {
   const uint64_t seed =
@@ -104,6 +122,7 @@ __device__ __forceinline__ void check_smem_alignment(const void* smem) {
 }
 
 // ============================================================================== forward
+template <int MODE>
 __global__ void __launch_bounds__(kAttnThreads)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -125,7 +144,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
   const int qb = blockIdx.x, bh = blockIdx.y;
   const int b = bh / p.heads, h = bh % p.heads;
   const int row0 = b * p.S;
-  const int nkv = p.causal ? qb + 1 : p.S / 128;
+  const bool is_causal = MODE < 0 ? p.causal != 0 : (MODE & 1) != 0;
+  const int nkv = is_causal ? qb + 1 : p.S / 128;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
@@ -141,6 +161,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();
   const uint32_t tS = tmem, tO = tmem + 128;
 
   if (warp == 0) {
@@ -187,7 +209,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     const float scale_l2 = p.scale * kLog2e;
     const float slope_l2 = p.alibi != nullptr ? p.alibi[h] * kLog2e : 0.f;
     const DropRng rng = attn_rng(p);
-    const float* kb = p.key_bias != nullptr ? p.key_bias + static_cast<size_t>(b) * p.S : nullptr;
+    const AttnFlags<MODE> f(p, rng);
+    const float* kb = f.kbias ? p.key_bias + static_cast<size_t>(b) * p.S : nullptr;
     float m = -INFINITY, l = 0.f;  // l: partial row sum over this thread's columns
     uint32_t regs[32];
     float v[32];
@@ -196,9 +219,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       tc_fence_after();
       auto score = [&](uint32_t raw, int jk) -> float {
         float x = __uint_as_float(raw) * scale_l2;
-        if (p.alibi != nullptr) x += slope_l2 * static_cast<float>(jk - iq);
-        if (kb != nullptr) x += kb[jk] * kLog2e;
-        if (p.causal && jk > iq) x = -INFINITY;
+        if (f.alibi) x += slope_l2 * static_cast<float>(jk - iq);
+        if (f.kbias) x += kb[jk] * kLog2e;
+        if (f.causal && jk > iq) x = -INFINITY;
         return x;
       };
       float mx = -INFINITY;
@@ -219,7 +242,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       const float mx_blk = fmaxf(__bfloat162float(sMax[r]), __bfloat162float(sMax[128 + r]));
       const float m_new = fmaxf(m, mx_blk);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float corr = exp2f(m - m_use);
+      const float corr = ex2_approx(m - m_use);
       if (j > 0) {  // previous P·V must have finished reading sP and updating O
         mbar_wait(o_full, (j - 1) & 1);
         tc_fence_after();
@@ -232,11 +255,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
         tmem_ld_wait();
 #pragma unroll
         for (int t = 0; t < 32; ++t) {
-          const float pr = exp2f(score(regs[t], j * 128 + col + t) - m_use);
+          const float pr = ex2_approx(score(regs[t], j * 128 + col + t) - m_use);
           rs += pr;
           v[t] = pr;
         }
-        if (rng.thr != 0u) {
+        if (f.drop) {
           float ks[32];
           attn_keep32(rng, p, bh, iq, j * 128 + col, ks);
 #pragma unroll
@@ -293,6 +316,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
                   float* __restrict__ delta, int B, int S, int heads) {
+  pdl_trigger();
+  pdl_wait();
   const int tok = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (tok >= B * S) return;
   const int lane = threadIdx.x & 31;
@@ -309,6 +334,7 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __re
 }
 
 // ============================================================================== backward: dQ
+template <int MODE>
 __global__ void __launch_bounds__(kAttnThreads)
 attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
                    const AttnParams p) {
@@ -331,7 +357,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   const int qb = blockIdx.x, bh = blockIdx.y;
   const int b = bh / p.heads, h = bh % p.heads;
   const int row0 = b * p.S;
-  const int nkv = p.causal ? qb + 1 : p.S / 128;
+  const bool is_causal = MODE < 0 ? p.causal != 0 : (MODE & 1) != 0;
+  const int nkv = is_causal ? qb + 1 : p.S / 128;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tm_qkv);
@@ -348,6 +375,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();
   const uint32_t tS = tmem, tdP = tmem + 128, tdQ = tmem + 256;
 
   if (warp == 0) {
@@ -397,9 +426,11 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
     const float scale_l2 = p.scale * kLog2e;
     const float slope_l2 = p.alibi != nullptr ? p.alibi[h] * kLog2e : 0.f;
     const DropRng rng = attn_rng(p);
-    const float* kb = p.key_bias != nullptr ? p.key_bias + static_cast<size_t>(b) * p.S : nullptr;
+    const AttnFlags<MODE> f(p, rng);
+    const float* kb = f.kbias ? p.key_bias + static_cast<size_t>(b) * p.S : nullptr;
     const float lse = p.lse[static_cast<size_t>(bh) * p.S + iq];
-    const float lse_l2 = lse * kLog2e;
+    // a fully masked row has lse = -inf: +inf here makes every probability exp2(x - inf) = 0
+    const float lse_l2 = lse == -INFINITY ? INFINITY : lse * kLog2e;
     const float dlt = p.delta[static_cast<size_t>(bh) * p.S + iq];
     uint32_t rs[32], rp[32];
     float v[32];
@@ -417,18 +448,18 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
         tmem_ld_32x32(tdP + lane_off + col, rp);
         tmem_ld_wait();
         float ks[32];
-        if (rng.thr != 0u) attn_keep32(rng, p, bh, iq, j * 128 + col, ks);
+        if (f.drop) attn_keep32(rng, p, bh, iq, j * 128 + col, ks);
 #pragma unroll
         for (int t = 0; t < 32; ++t) {
           const int jk = j * 128 + col + t;
           float x = __uint_as_float(rs[t]) * scale_l2;
-          if (p.alibi != nullptr) x += slope_l2 * static_cast<float>(jk - iq);
-          if (kb != nullptr) x += kb[jk] * kLog2e;
-          float pr = exp2f(x - lse_l2);
-          if ((p.causal && jk > iq) || lse == -INFINITY) pr = 0.f;
+          if (f.alibi) x += slope_l2 * static_cast<float>(jk - iq);
+          if (f.kbias) x += kb[jk] * kLog2e;
+          float pr = ex2_approx(x - lse_l2);
+          if (f.causal && jk > iq) pr = 0.f;
           float dp = __uint_as_float(rp[t]);
-          if (rng.thr != 0u) dp *= ks[t];
-          v[t] = pr * (dp - dlt) * p.scale;
+          if (f.drop) dp *= ks[t];
+          v[t] = (pr * p.scale) * (dp - dlt);
         }
         store_chunk_sw128(sdS, r, col, v);
       }
@@ -457,6 +488,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
 }
 
 // ============================================================================== backward: dK, dV
+template <int MODE>
 __global__ void __launch_bounds__(kAttnThreads)
 attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
                      const __grid_constant__ CUtensorMap tm_do, const AttnParams p) {
@@ -483,7 +515,8 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
   const int b = bh / p.heads, h = bh % p.heads;
   const int row0 = b * p.S;
   const int nq = p.S / 128;
-  const int i0 = p.causal ? kb_idx : 0;  // first query block that can see these keys
+  const bool is_causal = MODE < 0 ? p.causal != 0 : (MODE & 1) != 0;
+  const int i0 = is_causal ? kb_idx : 0;  // first query block that can see these keys
   const int niter = nq - i0;
 
   if (warp == 0 && lane == 0) {
@@ -501,6 +534,8 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();
   const uint32_t tST = tmem, tdPT = tmem + 128, tdK = tmem + 256, tdV = tmem + 320;
 
   if (warp == 0) {
@@ -553,8 +588,12 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
     const float scale_l2 = p.scale * kLog2e;
     const float slope_l2 = p.alibi != nullptr ? p.alibi[h] * kLog2e : 0.f;
     const DropRng rng = attn_rng(p);
-    const float kbias_l2 =
-        p.key_bias != nullptr ? p.key_bias[static_cast<size_t>(b) * p.S + jk] * kLog2e : 0.f;
+    const AttnFlags<MODE> f(p, rng);
+    const float kbias_l2 = f.kbias ? p.key_bias[static_cast<size_t>(b) * p.S + jk] * kLog2e : 0.f;
+    // dropout hash state: pairs of adjacent keys share one 32-bit hash; consecutive queries are
+    // S/2 pairs apart.  The key derivation only depends on the high word of the pair index, which
+    // changes at most once over a thread's whole query range: re-derived on change.
+    uint32_t drop_hi = 0xFFFFFFFFu, drop_k = 0u;
     uint32_t rs[32], rp[32];
     float vp[32], vd[32];
     for (int it = 0; it < niter; ++it) {
@@ -562,7 +601,8 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
       // per-query statistics of this query block -> smem (previous readers are done: they
       // passed the named barrier at the end of the last iteration)
       if (half == 0) {
-        sLse[r] = p.lse[static_cast<size_t>(bh) * p.S + i * 128 + r] * kLog2e;
+        const float lse = p.lse[static_cast<size_t>(bh) * p.S + i * 128 + r];
+        sLse[r] = lse == -INFINITY ? INFINITY : lse * kLog2e;  // fully masked row: exp2(x - inf) = 0
         sDelta[r] = p.delta[static_cast<size_t>(bh) * p.S + i * 128 + r];
       }
       named_bar_sync(1, 256);
@@ -578,17 +618,29 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
         tmem_ld_32x32(tST + lane_off + col, rs);
         tmem_ld_32x32(tdPT + lane_off + col, rp);
         tmem_ld_wait();
+        // element index of (query iq0, key jk); query iq0 + t is t * S elements further
+        const uint64_t idx0 = (static_cast<uint64_t>(bh) * p.S + (i * 128 + col)) * p.S + jk;
 #pragma unroll
         for (int t = 0; t < 32; ++t) {
           const int iq = i * 128 + col + t;
           float x = __uint_as_float(rs[t]) * scale_l2 + kbias_l2;
-          if (p.alibi != nullptr) x += slope_l2 * static_cast<float>(jk - iq);
-          const float l2 = sLse[col + t];
-          float pr = exp2f(x - l2);
-          if ((p.causal && jk > iq) || l2 == -INFINITY) pr = 0.f;
-          const float keep = rng.thr != 0u ? attn_keep1(rng, p, bh, iq, jk) : 1.f;
+          if (f.alibi) x += slope_l2 * static_cast<float>(jk - iq);
+          float pr = ex2_approx(x - sLse[col + t]);
+          if (f.causal && jk > iq) pr = 0.f;
+          float keep = 1.f;
+          if (f.drop) {
+            const uint64_t pair = (idx0 + static_cast<uint64_t>(t) * p.S) >> 1;
+            const uint32_t hi = static_cast<uint32_t>(pair >> 32);
+            if (hi != drop_hi) {
+              drop_hi = hi;
+              drop_k = drop_key(rng, hi);
+            }
+            const uint32_t bits = drop_bits_keyed(drop_k, static_cast<uint32_t>(pair));
+            const uint32_t u = (jk & 1) ? (bits >> 16) : (bits & 0xFFFFu);
+            keep = u >= rng.thr ? rng.inv_keep : 0.f;
+          }
           vp[t] = pr * keep;
-          vd[t] = pr * (__uint_as_float(rp[t]) * keep - sDelta[col + t]) * p.scale;
+          vd[t] = (pr * p.scale) * (__uint_as_float(rp[t]) * keep - sDelta[col + t]);
         }
         store_chunk_sw128(sPT, r, col, vp);
         store_chunk_sw128(sdST, r, col, vd);
@@ -641,6 +693,69 @@ static int check_attn_args(int B, int S, int heads, int head_dim, int ld_qkv) {
   return 0;
 }
 
+// ------------------------------------------------------------------ host-side mode dispatch
+// Specialised instances cover the shipped model families in training (dropout on) plus plain
+// BERT; anything else runs the generic instance (MODE = -1).
+static int attn_mode(int causal, const float* alibi, float p_drop, const float* key_bias) {
+  const int m = (causal ? 1 : 0) | (alibi != nullptr ? 2 : 0) | (p_drop > 0.f ? 4 : 0) |
+                (key_bias != nullptr ? 8 : 0);
+  switch (m) {
+    case 0: case 4: case 12: case 5: case 7: return m;
+    default: return -1;
+  }
+}
+#define DTDS_ATTN_DISPATCH(mode, CALL)            \
+  switch (mode) {                                 \
+    case 0: { constexpr int M = 0; CALL; } break;   \
+    case 4: { constexpr int M = 4; CALL; } break;   \
+    case 12: { constexpr int M = 12; CALL; } break; \
+    case 5: { constexpr int M = 5; CALL; } break;   \
+    case 7: { constexpr int M = 7; CALL; } break;   \
+    default: { constexpr int M = -1; CALL; } break; \
+  }
+
+static int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev & 63;
+}
+
+template <int MODE>
+static int launch_attn_fwd(dim3 grid, cudaStream_t stream, const CUtensorMap& tm, const AttnParams& p) {
+  static bool attr_set[64] = {};   // function attributes are per device
+  const int dev = current_device();
+  if (!attr_set[dev]) {
+    DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_fwd_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
+    attr_set[dev] = true;
+  }
+  DTDS_HOST_CHECK(launch_pdl(attn_fwd_kernel<MODE>, grid, dim3(kAttnThreads), kFwdSmem, stream, tm, p));
+  return 0;
+}
+template <int MODE>
+static int launch_attn_dkdv(dim3 grid, cudaStream_t stream, const CUtensorMap& tm, const CUtensorMap& tmdo,
+                            const AttnParams& p) {
+  static bool attr_set[64] = {};
+  const int dev = current_device();
+  if (!attr_set[dev]) {
+    DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_bwd_dkdv_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDkdvSmem));
+    attr_set[dev] = true;
+  }
+  DTDS_HOST_CHECK(launch_pdl(attn_bwd_dkdv_kernel<MODE>, grid, dim3(kAttnThreads), kDkdvSmem, stream, tm, tmdo, p));
+  return 0;
+}
+template <int MODE>
+static int launch_attn_dq(dim3 grid, cudaStream_t stream, const CUtensorMap& tm, const CUtensorMap& tmdo,
+                          const AttnParams& p) {
+  static bool attr_set[64] = {};
+  const int dev = current_device();
+  if (!attr_set[dev]) {
+    DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDqSmem));
+    attr_set[dev] = true;
+  }
+  DTDS_HOST_CHECK(launch_pdl(attn_bwd_dq_kernel<MODE>, grid, dim3(kAttnThreads), kDqSmem, stream, tm, tmdo, p));
+  return 0;
+}
+
 }  // namespace dtds
 
 using namespace dtds;
@@ -659,15 +774,10 @@ extern "C" int dtds_attention_fwd(const void* qkv, int ld_qkv, void* out, float*
   p.B = B; p.S = S; p.heads = heads; p.H = H; p.scale = scale; p.causal = causal;
   p.key_bias = key_bias; p.alibi = alibi_slopes; p.p_drop = p_drop; p.seed = seed; p.seed_dev = seed_dev;
   p.out = static_cast<__nv_bfloat16*>(out); p.lse = lse;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));
-    attr_set = true;
-  }
   dim3 grid(S / 128, B * heads);
-  attn_fwd_kernel<<<grid, kAttnThreads, kFwdSmem, stream>>>(tm, p);
-  DTDS_HOST_CHECK(cudaGetLastError());
-  return 0;
+  const int mode = attn_mode(causal, alibi_slopes, p_drop, key_bias);
+  DTDS_ATTN_DISPATCH(mode, rc = launch_attn_fwd<M>(grid, stream, tm, p));
+  return rc;
 }
 
 extern "C" int dtds_attention_bwd_parts(const void* qkv, int ld_qkv, const void* out, const void* dout,
@@ -705,25 +815,20 @@ extern "C" int dtds_attention_bwd_parts(const void* qkv, int ld_qkv, const void*
   p.B = B; p.S = S; p.heads = heads; p.H = H; p.scale = scale; p.causal = causal;
   p.key_bias = key_bias; p.alibi = alibi_slopes; p.p_drop = p_drop; p.seed = seed; p.seed_dev = seed_dev;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
-  static bool attr_set = false;
-  if (!attr_set) {
-    DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDqSmem));
-    DTDS_HOST_CHECK(cudaFuncSetAttribute(attn_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDkdvSmem));
-    attr_set = true;
-  }
+  const int mode = attn_mode(causal, alibi_slopes, p_drop, key_bias);
   if (parts & 1) {
-    attn_delta_kernel<<<(B * S + 7) / 8, 256, 0, stream>>>(
-        static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), delta, B, S, heads);
-    DTDS_HOST_CHECK(cudaGetLastError());
+    DTDS_HOST_CHECK(launch_pdl(attn_delta_kernel, dim3((B * S + 7) / 8), dim3(256), 0, stream,
+                               static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout),
+                               delta, B, S, heads));
   }
   dim3 grid(S / 128, B * heads);
   if (parts & 2) {
-    attn_bwd_dkdv_kernel<<<grid, kAttnThreads, kDkdvSmem, stream>>>(tm, tmdo, p);
-    DTDS_HOST_CHECK(cudaGetLastError());
+    DTDS_ATTN_DISPATCH(mode, rc = launch_attn_dkdv<M>(grid, stream, tm, tmdo, p));
+    if (rc) return rc;
   }
   if (parts & 4) {
-    attn_bwd_dq_kernel<<<grid, kAttnThreads, kDqSmem, stream>>>(tm, tmdo, p);
-    DTDS_HOST_CHECK(cudaGetLastError());
+    DTDS_ATTN_DISPATCH(mode, rc = launch_attn_dq<M>(grid, stream, tm, tmdo, p));
+    if (rc) return rc;
   }
   return 0;
 }

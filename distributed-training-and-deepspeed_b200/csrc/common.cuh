@@ -6,6 +6,8 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
+#include <utility>
 
 #define DTDS_HOST_CHECK(expr)                                                            \
   do {                                                                                   \
@@ -377,10 +379,17 @@ __device__ __forceinline__ DropRng make_drop_rng(uint64_t seed, float p) {
   r.inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   return r;
 }
+// The key only depends on the high word of the pair index: callers that walk a range of pairs
+// derive it once (drop_key) and hash the low word per pair (drop_bits_keyed).
+__device__ __forceinline__ uint32_t drop_key(const DropRng& r, uint32_t pair_hi) {
+  return r.seed_lo ^ mix32(r.seed_hi + pair_hi * 0x85EBCA77u);
+}
+__device__ __forceinline__ uint32_t drop_bits_keyed(uint32_t key, uint32_t pair_lo) {
+  return mix32(key ^ (pair_lo * 0x9E3779B1u));
+}
 // 32 random bits covering elements 2*pair and 2*pair+1.
 __device__ __forceinline__ uint32_t drop_bits(const DropRng& r, uint64_t pair) {
-  const uint32_t key = r.seed_lo ^ mix32(r.seed_hi + static_cast<uint32_t>(pair >> 32) * 0x85EBCA77u);
-  return mix32(key ^ (static_cast<uint32_t>(pair) * 0x9E3779B1u));
+  return drop_bits_keyed(drop_key(r, static_cast<uint32_t>(pair >> 32)), static_cast<uint32_t>(pair));
 }
 // Keep-scale of a single element (slow path: scalar tails).
 __device__ __forceinline__ float drop_scale1(const DropRng& r, uint64_t idx) {
@@ -424,6 +433,40 @@ __device__ __forceinline__ float act_grad(float x, int act) {
     case ACT_GELU_TANH: return gelu_tanh_grad(x);
     default: return 1.f;
   }
+}
+
+// ---------------------------------------------------------------- programmatic dependent launch
+// A kernel launched through launch_pdl may become resident while the previous kernel of the stream
+// is still draining: its prologue (barrier init, TMEM allocation, descriptor prefetch, CTA
+// scheduling) overlaps that tail.  pdl_wait() blocks until the previous grid has completed and its
+// writes are visible, so it must precede the first access to global memory; pdl_trigger() lets the
+// *next* kernel start its own prologue.  Both are no-ops for a kernel launched the ordinary way.
+// DTDS_PDL=0 turns the launch attribute off (every launch fully serialised again).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+  static const int on = [] {
+    const char* e = getenv("DTDS_PDL");
+    return e == nullptr ? 1 : atoi(e);
+  }();
+  return on != 0;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
 }  // namespace dtds

@@ -200,6 +200,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();   // operands, bias/residual and the output buffer belong to earlier kernels until here
   if (dbg != nullptr && threadIdx.x == 0) dbg[1] = clock64();  // setup done
 
   if (warp == 0) {
@@ -522,7 +524,8 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   int grid = sm_count();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (num_tiles < grid && !FETCH) grid = num_tiles;  // fetch mode keeps every SM pulling chunks
-  kern<<<grid, kGemmThreads + (FETCH ? kFetchThreads : 0), Cfg::kSmemBytes, stream>>>(tmA, tmB, p);
+  DTDS_HOST_CHECK(launch_pdl(kern, dim3(grid), dim3(kGemmThreads + (FETCH ? kFetchThreads : 0)),
+                             Cfg::kSmemBytes, stream, tmA, tmB, p));
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }

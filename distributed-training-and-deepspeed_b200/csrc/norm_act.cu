@@ -22,6 +22,8 @@ ln_fwd_warp_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
                    __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ z_out,
                    float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int cols,
                    float eps, float p_drop, uint64_t seed, const uint64_t* __restrict__ seed_dev) {
+  pdl_trigger();
+  pdl_wait();
   if (seed_dev != nullptr) seed += *seed_dev * 0xD1B54A32D192ED03ull;
   const int warps_per_block = blockDim.x >> 5;
   const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
@@ -121,6 +123,8 @@ ln_fwd_block_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
                     __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ z_out,
                     float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int cols,
                     float eps, float p_drop, uint64_t seed, const uint64_t* __restrict__ seed_dev) {
+  pdl_trigger();
+  pdl_wait();
   if (seed_dev != nullptr) seed += *seed_dev * 0xD1B54A32D192ED03ull;
   __shared__ float scratch[32];
   const int row = blockIdx.x;
@@ -201,6 +205,8 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
               __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ dx_drop,
               float* __restrict__ partial, int rows, int cols, float p_drop, uint64_t seed,
               const uint64_t* __restrict__ seed_dev) {
+  pdl_trigger();
+  pdl_wait();
   if (seed_dev != nullptr) seed += *seed_dev * 0xD1B54A32D192ED03ull;
   extern __shared__ float sm[];  // [2][cols] block-level dgamma/dbeta accumulators
   float* s_dg = sm;
@@ -314,6 +320,8 @@ ln_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __re
                  const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ dz_extra,
                  __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ dx_drop, int rows, int cols,
                  float p_drop, uint64_t seed, const uint64_t* __restrict__ seed_dev) {
+  pdl_trigger();
+  pdl_wait();
   if (seed_dev != nullptr) seed += *seed_dev * 0xD1B54A32D192ED03ull;
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -372,6 +380,8 @@ __global__ void __launch_bounds__(256)
 ln_bwd_dgb_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ z,
                   const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ partial,
                   int rows, int cols) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sg[8][64], sb[8][64];
   const int c0 = blockIdx.x * 64;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -412,6 +422,8 @@ __global__ void __launch_bounds__(256)
 ln_bwd_finalize_kernel(const float* __restrict__ partial, int nblocks, int cols,
                        void* __restrict__ dgamma, void* __restrict__ dbeta, int out_fp32,
                        int accumulate) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float s[8][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + tx;
@@ -452,6 +464,8 @@ __global__ void __launch_bounds__(256)
 colsum_kernel(const __nv_bfloat16* __restrict__ x, int rows, int cols, int ld,
               float* __restrict__ scratch, unsigned int* __restrict__ counters,
               void* __restrict__ out, int out_fp32, int accumulate) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float s[8][64];
   __shared__ bool is_last;
   const int c0 = blockIdx.x * 64;
@@ -658,15 +672,14 @@ extern "C" int dtds_layernorm_fwd(const void* x, const void* residual, const voi
   const int wpb = 8;
   const int grid = (rows + wpb - 1) / wpb;
   if (cols <= 256) {
-    ln_fwd_warp_kernel<1><<<grid, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev));
+    DTDS_HOST_CHECK(launch_pdl(ln_fwd_warp_kernel<1>, dim3(grid), dim3(256), 0, stream, X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev)));
   } else if (cols <= 768) {
-    ln_fwd_warp_kernel<3><<<grid, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev));
+    DTDS_HOST_CHECK(launch_pdl(ln_fwd_warp_kernel<3>, dim3(grid), dim3(256), 0, stream, X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev)));
   } else if (cols <= 1024) {
-    ln_fwd_warp_kernel<4><<<grid, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev));
+    DTDS_HOST_CHECK(launch_pdl(ln_fwd_warp_kernel<4>, dim3(grid), dim3(256), 0, stream, X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev)));
   } else {
-    ln_fwd_block_kernel<<<rows, 256, 0, stream>>>(X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev));
+    DTDS_HOST_CHECK(launch_pdl(ln_fwd_block_kernel, dim3(rows), dim3(256), 0, stream, X, R, G, Bt, Y, Z, mean, rstd, rows, cols, eps, p_drop, seed, reinterpret_cast<const uint64_t*>(seed_dev)));
   }
-  DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }
 
@@ -692,21 +705,19 @@ extern "C" int dtds_layernorm_bwd(const void* dy, const void* z, const float* me
   if (cols % 8 != 0) return -1;
   const int blocks = dtds_layernorm_bwd_blocks(rows, cols);
   if (rows <= 64 * dtds::sm_count() && cols % 2 == 0) {
-    ln_bwd_dx_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(
+    DTDS_HOST_CHECK(launch_pdl(
+        ln_bwd_dx_kernel, dim3((rows + 7) / 8), dim3(256), 0, stream,
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(z), mean, rstd,
         static_cast<const __nv_bfloat16*>(gamma), static_cast<const __nv_bfloat16*>(dz_extra),
         static_cast<__nv_bfloat16*>(dz), static_cast<__nv_bfloat16*>(dx_drop), rows, cols, p_drop, seed,
-        reinterpret_cast<const uint64_t*>(seed_dev));
-    DTDS_HOST_CHECK(cudaGetLastError());
+        reinterpret_cast<const uint64_t*>(seed_dev)));
     if (dgamma != nullptr && dbeta != nullptr) {
       dim3 grid((cols + 63) / 64, blocks);
-      ln_bwd_dgb_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(dy),
-                                                  static_cast<const __nv_bfloat16*>(z), mean, rstd, partial,
-                                                  rows, cols);
-      DTDS_HOST_CHECK(cudaGetLastError());
-      ln_bwd_finalize_kernel<<<(2 * cols + 31) / 32, 256, 0, stream>>>(partial, blocks, cols, dgamma, dbeta,
-                                                                       grads_fp32, accumulate);
-      DTDS_HOST_CHECK(cudaGetLastError());
+      DTDS_HOST_CHECK(launch_pdl(ln_bwd_dgb_kernel, grid, dim3(256), 0, stream,
+                                 static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(z),
+                                 mean, rstd, partial, rows, cols));
+      DTDS_HOST_CHECK(launch_pdl(ln_bwd_finalize_kernel, dim3((2 * cols + 31) / 32), dim3(256), 0, stream,
+                                 partial, blocks, cols, dgamma, dbeta, grads_fp32, accumulate));
     }
     return 0;
   }
@@ -753,9 +764,8 @@ extern "C" int dtds_colsum(const void* x, int rows, int cols, int ld,
   dim3 grid(tiles, splits);
   // per-tile arrival counters live right after the partial sums (same zeroed scratch)
   unsigned int* counters = reinterpret_cast<unsigned int*>(scratch + tiles * 64);
-  colsum_kernel<<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), rows, cols, ld, scratch,
-                                          counters, out, out_fp32, accumulate);
-  DTDS_HOST_CHECK(cudaGetLastError());
+  DTDS_HOST_CHECK(launch_pdl(colsum_kernel, grid, dim3(256), 0, stream, static_cast<const __nv_bfloat16*>(x),
+                             rows, cols, ld, scratch, counters, out, out_fp32, accumulate));
   return 0;
 }
 
