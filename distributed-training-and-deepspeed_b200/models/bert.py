@@ -64,10 +64,11 @@ class BertLayer(nn.Module):
         self.output_ln = LayerNorm(H, cfg.layer_norm_eps, cfg.hidden_dropout_prob)
 
     def forward(self, x, key_bias=None):
-        a = self.attention(x, key_bias)
-        h = self.attention_ln(a, residual=x)
-        f = self.mlp(h)
-        return self.output_ln(f, residual=h)
+        # fork: the skip branch's gradient is added in the dgrad GEMM epilogue of the main branch
+        a, x_skip = self.attention(x, key_bias, fork=True)
+        h = self.attention_ln(a, residual=x_skip)
+        f, h_skip = self.mlp(h, fork=True)
+        return self.output_ln(f, residual=h_skip)
 
 
 class BertOnlyMLMHead(nn.Module):

@@ -38,10 +38,13 @@ class DecoderLayer(nn.Module):
 
     def forward(self, x, key_bias=None):
         fuse_res = not (self.training and self.drop.p > 0.0)
-        a = self.attention(self.input_ln(x), key_bias, residual=x if fuse_res else None)
-        h = a if fuse_res else self.drop(a, residual=x)
-        f = self.mlp(self.post_attention_ln(h), residual=h if fuse_res else None)
-        return f if fuse_res else self.drop(f, residual=h)
+        # fork: the skip branch's gradient is added inside the LayerNorm backward kernel
+        n, x_skip = self.input_ln(x, fork=True)
+        a = self.attention(n, key_bias, residual=x_skip if fuse_res else None)
+        h = a if fuse_res else self.drop(a, residual=x_skip)
+        n2, h_skip = self.post_attention_ln(h, fork=True)
+        f = self.mlp(n2, residual=h_skip if fuse_res else None)
+        return f if fuse_res else self.drop(f, residual=h_skip)
 
 
 class CausalLM(nn.Module):

@@ -33,8 +33,8 @@ class Linear(nn.Module):
         self.weight = nn.Parameter(_init_normal_(torch.empty(out_features, in_features), init_std))
         self.bias = nn.Parameter(torch.zeros(out_features)) if bias else None
 
-    def forward(self, x, residual=None):
-        return Fn.linear(x, self.weight, self.bias, self.act, residual)
+    def forward(self, x, residual=None, fork=False):
+        return Fn.linear(x, self.weight, self.bias, self.act, residual, fork)
 
     def extra_repr(self):
         return f"in={self.in_features}, out={self.out_features}, bias={self.bias is not None}, act={self.act}"
@@ -50,8 +50,8 @@ class LayerNorm(nn.Module):
         self.weight = nn.Parameter(torch.ones(hidden))
         self.bias = nn.Parameter(torch.zeros(hidden))
 
-    def forward(self, x, residual=None):
-        return Fn.layer_norm(x, self.weight, self.bias, self.eps, residual, self.p_drop, self.training)
+    def forward(self, x, residual=None, fork=False):
+        return Fn.layer_norm(x, self.weight, self.bias, self.eps, residual, self.p_drop, self.training, fork)
 
 
 class MLP(nn.Module):
@@ -61,8 +61,8 @@ class MLP(nn.Module):
         self.fc1 = Linear(hidden, ffn, bias=bias)
         self.fc2 = Linear(ffn, hidden, bias=bias)
 
-    def forward(self, x, residual=None):
-        return Fn.mlp(x, self.fc1.weight, self.fc1.bias, self.fc2.weight, self.fc2.bias, self.act, residual)
+    def forward(self, x, residual=None, fork=False):
+        return Fn.mlp(x, self.fc1.weight, self.fc1.bias, self.fc2.weight, self.fc2.bias, self.act, residual, fork)
 
 
 def alibi_slopes(num_heads: int) -> torch.Tensor:
@@ -104,12 +104,19 @@ class SelfAttention(nn.Module):
             self._alibi_by_device[device] = t
         return t
 
-    def forward(self, x, key_bias=None, residual=None):
+    def forward(self, x, key_bias=None, residual=None, fork=False):
+        """``fork=True`` returns ``(out, x_skip)`` (see ops.functional.linear)."""
         B, S, H = x.shape
-        qkv = self.qkv(x).view(B * S, 3 * H)
+        x_skip = None
+        if fork:
+            qkv, x_skip = self.qkv(x, fork=True)
+            qkv = qkv.view(B * S, 3 * H)
+        else:
+            qkv = self.qkv(x).view(B * S, 3 * H)
         ctx = Fn.attention(qkv, B, S, self.heads, causal=self.causal, key_bias=key_bias,
                            alibi=self.alibi_on(x.device), p_drop=self.p_drop, training=self.training)
-        return self.out(ctx.view(B, S, H), residual)
+        out = self.out(ctx.view(B, S, H), residual)
+        return (out, x_skip) if fork else out
 
 
 class Dropout(nn.Module):

@@ -162,10 +162,11 @@ class LinearFn(torch.autograd.Function):
     MN-major) written into the flat gradient buffer, bias column-sum."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, act, residual):
+    def forward(ctx, x, weight, bias, act, residual, fork=False):
         shape = x.shape
         x2 = x.reshape(-1, shape[-1])
         N = weight.shape[0]
+        ctx.fork = fork
         need_pre = act != ACT_NONE and any(ctx.needs_input_grad)
         pre = torch.empty(x2.shape[0], N, dtype=x2.dtype, device=x2.device) if need_pre else None
         res2 = residual.reshape(-1, N) if residual is not None else None
@@ -181,10 +182,12 @@ class LinearFn(torch.autograd.Function):
         ctx.act = act
         ctx.has_res = residual is not None
         ctx.in_shape = shape
+        if fork:   # second handle on the input for a skip connection (see `linear`)
+            return y.view(*shape[:-1], N), x.view_as(x)
         return y.view(*shape[:-1], N)
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dskip=None):
         x2, weight, bias, pre = ctx.saved_tensors
         N = weight.shape[0]
         dy2 = dy.reshape(-1, N)
@@ -194,19 +197,37 @@ class LinearFn(torch.autograd.Function):
         du = K.act_bwd(dy2, pre, ctx.act) if ctx.act != ACT_NONE else dy2
         dx = None
         if ctx.needs_input_grad[0]:
+            # gradient of the skip branch: added in the epilogue of the dgrad GEMM
+            dsk2 = _as2d(dskip, x2.shape[1]) if dskip is not None else None
             if getattr(weight, "_ag_pending", False):   # ZeRO-3 re-gather fused with the dgrad GEMM
                 dx = K.gemm_allgather(du, weight.data, weight._ag_spec, b_mn_major=True).view(ctx.in_shape)
                 weight._ag_pending = False
+                if dsk2 is not None:
+                    dx = dx + dskip
             else:
-                dx = K.gemm(du, weight, b_mn_major=True).view(ctx.in_shape)
+                dx = K.gemm(du, weight, b_mn_major=True, residual=dsk2).view(ctx.in_shape)
         with _OnSideStream(du, x2, params=(weight, bias)):
             dw = _wgrad(du, x2, weight) if ctx.needs_input_grad[1] else None
             db = _bgrad(du, bias) if (bias is not None and ctx.needs_input_grad[2]) else None
-        return dx, dw, db, None, dres
+        return dx, dw, db, None, dres, None
 
 
-def linear(x, weight, bias=None, act=ACT_NONE, residual=None):
-    return LinearFn.apply(x, weight, bias, act, residual)
+FUSE_SKIP_GRADS = __import__("os").environ.get("DTDS_FUSE_SKIP_GRADS", "1") != "0"
+
+
+def _as2d(t, cols):
+    t2 = t.reshape(-1, cols)
+    return t2 if t2.is_contiguous() else t2.contiguous()
+
+
+def linear(x, weight, bias=None, act=ACT_NONE, residual=None, fork=False):
+    """``fork=True`` returns ``(y, x_skip)``: x_skip is x again, to be used as the residual of a
+    later op.  Its gradient comes back to this function's backward as a separate argument and is
+    added in the epilogue of the dgrad GEMM, instead of autograd summing the two branches of x
+    with a standalone elementwise kernel.  (FUSE_SKIP_GRADS = False: plain autograd, for A/B.)"""
+    if fork and not FUSE_SKIP_GRADS:
+        return LinearFn.apply(x, weight, bias, act, residual, False), x
+    return LinearFn.apply(x, weight, bias, act, residual, fork)
 
 
 # --------------------------------------------------------------------------------------- MLP
@@ -215,7 +236,7 @@ class MLPFn(torch.autograd.Function):
     the epilogue of the W2 dgrad GEMM (du = (df·W2) ⊙ act'(u)); no standalone elementwise pass."""
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2, act, residual):
+    def forward(ctx, x, w1, b1, w2, b2, act, residual, fork=False):
         shape = x.shape
         x2 = x.reshape(-1, shape[-1])
         M, F = x2.shape[0], w1.shape[0]
@@ -227,10 +248,12 @@ class MLPFn(torch.autograd.Function):
         ctx.act = act
         ctx.has_res = residual is not None
         ctx.in_shape = shape
+        if fork:
+            return f.view(*shape[:-1], w2.shape[0]), x.view_as(x)
         return f.view(*shape[:-1], w2.shape[0])
 
     @staticmethod
-    def backward(ctx, df):
+    def backward(ctx, df, dskip=None):
         x2, w1, b1, w2, b2, u, a = ctx.saved_tensors
         df2 = df.reshape(-1, w2.shape[0])
         if not df2.is_contiguous():
@@ -241,15 +264,21 @@ class MLPFn(torch.autograd.Function):
         with _OnSideStream(df2, a, params=(w2, b2)):
             dw2 = _wgrad(df2, a, w2)
             db2 = _bgrad(df2, b2) if b2 is not None else None
-        dx = K.gemm(du, w1, b_mn_major=True).view(ctx.in_shape) if ctx.needs_input_grad[0] else None
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dsk2 = _as2d(dskip, x2.shape[1]) if dskip is not None else None
+            dx = K.gemm(du, w1, b_mn_major=True, residual=dsk2).view(ctx.in_shape)
         with _OnSideStream(du, x2, params=(w1, b1)):
             dw1 = _wgrad(du, x2, w1)
             db1 = _bgrad(du, b1) if b1 is not None else None
-        return dx, dw1, db1, dw2, db2, None, dres
+        return dx, dw1, db1, dw2, db2, None, dres, None
 
 
-def mlp(x, w1, b1, w2, b2, act, residual=None):
-    return MLPFn.apply(x, w1, b1, w2, b2, act, residual)
+def mlp(x, w1, b1, w2, b2, act, residual=None, fork=False):
+    """``fork=True``: see `linear`."""
+    if fork and not FUSE_SKIP_GRADS:
+        return MLPFn.apply(x, w1, b1, w2, b2, act, residual, False), x
+    return MLPFn.apply(x, w1, b1, w2, b2, act, residual, fork)
 
 
 # --------------------------------------------------------------------------------- LayerNorm
@@ -258,17 +287,21 @@ class LayerNormFn(torch.autograd.Function):
     in backward, never stored), one kernel + a tiny finalize backward."""
 
     @staticmethod
-    def forward(ctx, x, residual, gamma, beta, eps, p_drop, training):
+    def forward(ctx, x, residual, gamma, beta, eps, p_drop, training, fork=False):
         p = p_drop if training else 0.0
+        if fork:
+            assert residual is None and p == 0.0, "fork: plain LayerNorm(x) only"
         seed = next_seed() if p > 0.0 else 0
         y, z, mean, rstd = K.layernorm_fwd(x, residual, gamma, beta, eps, p, seed)
         ctx.save_for_backward(z, mean, rstd, gamma, beta)
         ctx.p, ctx.seed = p, seed
         ctx.has_res = residual is not None
+        if fork:   # pre-LN blocks: x also feeds the skip connection (see `linear`)
+            return y, x.view_as(x)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dskip=None):
         z, mean, rstd, gamma, beta = ctx.saved_tensors
         if not dy.is_contiguous():
             dy = dy.contiguous()
@@ -276,7 +309,7 @@ class LayerNormFn(torch.autograd.Function):
         mg_b, acc_b = grad_target(beta)
         direct = mg_g is not None and mg_b is not None and acc_g == acc_b
         dz, dxd, dg, db = K.layernorm_bwd(
-            dy, z, mean, rstd, gamma, p_drop=ctx.p, seed=ctx.seed,
+            dy, z, mean, rstd, gamma, dz_extra=dskip, p_drop=ctx.p, seed=ctx.seed,
             dgamma_out=mg_g if direct else None, dbeta_out=mg_b if direct else None,
             accumulate=acc_g if direct else False, want_dx_drop=True)
         if direct:
@@ -286,11 +319,15 @@ class LayerNormFn(torch.autograd.Function):
         else:
             dg = _emit(gamma, lambda out, acc: dg if out is None else (out.add_(dg) if acc else out.copy_(dg)))
             db = _emit(beta, lambda out, acc: db if out is None else (out.add_(db) if acc else out.copy_(db)))
-        return dxd, (dz if ctx.has_res else None), dg, db, None, None, None
+        return dxd, (dz if ctx.has_res else None), dg, db, None, None, None, None
 
 
-def layer_norm(x, gamma, beta, eps=1e-5, residual=None, p_drop=0.0, training=False):
-    return LayerNormFn.apply(x, residual, gamma, beta, eps, p_drop, training)
+def layer_norm(x, gamma, beta, eps=1e-5, residual=None, p_drop=0.0, training=False, fork=False):
+    """``fork=True`` (plain LN only): returns ``(y, x_skip)``; the skip gradient is added inside
+    the backward kernel (dz_extra) rather than by a standalone add."""
+    if fork and not FUSE_SKIP_GRADS:
+        return LayerNormFn.apply(x, residual, gamma, beta, eps, p_drop, training, False), x
+    return LayerNormFn.apply(x, residual, gamma, beta, eps, p_drop, training, fork)
 
 
 # --------------------------------------------------------------------------------- attention

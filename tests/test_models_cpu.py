@@ -143,3 +143,27 @@ def test_optimizer_built_before_ddp_wrap_follows_parameters():
     late, opt = _train_three_steps(ddp=True, opt_first=True)
     assert torch.equal(base, late)
     assert getattr(opt.flats[0], "_superseded_by", None) is None
+
+
+@pytest.mark.parametrize("name", ["bert-tiny", "bloom-tiny", "opt-tiny"])
+def test_fused_skip_gradients_match_autograd_sum(name):
+    """``fork=True`` outputs route the skip-branch gradient into the dgrad GEMM epilogue / the
+    LayerNorm backward; with the switch off autograd sums the two branches itself."""
+    from dtds_b200.ops import functional as Fn
+    torch.manual_seed(0)
+    cfg = get_config(name).replace(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    m = build_model(cfg)
+    ids = torch.randint(0, cfg.vocab_size, (2, 128))
+    grads = []
+    for fused in (True, False):
+        old = Fn.FUSE_SKIP_GRADS
+        Fn.FUSE_SKIP_GRADS = fused
+        try:
+            for p in m.parameters():
+                p.grad = None
+            m(ids, labels=ids).loss.backward()
+        finally:
+            Fn.FUSE_SKIP_GRADS = old
+        grads.append(torch.cat([p.grad.flatten() for p in m.parameters() if p.grad is not None]))
+    assert grads[0].shape == grads[1].shape and grads[0].abs().sum() > 0
+    torch.testing.assert_close(grads[0], grads[1], rtol=1e-4, atol=1e-6)
