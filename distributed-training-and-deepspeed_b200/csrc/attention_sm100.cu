@@ -82,6 +82,32 @@ __device__ __forceinline__ void attn_keep32(const DropRng& rng, const AttnParams
     ks[2 * k + 1] = (b >> 16) >= rng.thr ? rng.inv_keep : 0.f;
   }
 }
+// Transposed kernel (thread = key jk, registers = 32 consecutive queries starting at element index
+// idx0; consecutive queries are S elements apart).  The two keys of a hash pair sit in adjacent
+// lanes, so each lane hashes every other query and gets the rest from its neighbour: 16 hashes +
+// 16 shuffles per 32 scores instead of 32 hashes.  The key derivation only depends on the high
+// word of the pair index, which changes at most once over a thread's whole range (`hi`/`key` are
+// carried by the caller and re-derived on change).  Must be called by all 32 lanes.
+__device__ __forceinline__ void attn_keep32_t(const DropRng& rng, int S, uint64_t idx0, int lane,
+                                              uint32_t& hi_c, uint32_t& key_c, float (&ks)[32]) {
+  const int odd = lane & 1;  // == jk & 1: which half of the 32 hash bits is this key's
+#pragma unroll
+  for (int t = 0; t < 32; t += 2) {
+    const uint64_t pair = (idx0 + static_cast<uint64_t>(t + odd) * S) >> 1;
+    const uint32_t hi = static_cast<uint32_t>(pair >> 32);
+    if (hi != hi_c) {
+      hi_c = hi;
+      key_c = drop_key(rng, hi);
+    }
+    const uint32_t mine = drop_bits_keyed(key_c, static_cast<uint32_t>(pair));   // query t + odd
+    const uint32_t other = __shfl_xor_sync(0xffffffffu, mine, 1);                 // query t + 1 - odd
+    const uint32_t b0 = odd ? other : mine, b1 = odd ? mine : other;              // queries t, t + 1
+    const uint32_t u0 = odd ? (b0 >> 16) : (b0 & 0xFFFFu);
+    const uint32_t u1 = odd ? (b1 >> 16) : (b1 & 0xFFFFu);
+    ks[t] = u0 >= rng.thr ? rng.inv_keep : 0.f;
+    ks[t + 1] = u1 >= rng.thr ? rng.inv_keep : 0.f;
+  }
+}
 __device__ __forceinline__ DropRng attn_rng(const AttnParams& p) {
   const uint64_t seed =
       p.seed + (p.seed_dev != nullptr ? *p.seed_dev * 0xD1B54A32D192ED03ull : 0ull);
@@ -590,10 +616,7 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
     const DropRng rng = attn_rng(p);
     const AttnFlags<MODE> f(p, rng);
     const float kbias_l2 = f.kbias ? p.key_bias[static_cast<size_t>(b) * p.S + jk] * kLog2e : 0.f;
-    // dropout hash state: pairs of adjacent keys share one 32-bit hash; consecutive queries are
-    // S/2 pairs apart.  The key derivation only depends on the high word of the pair index, which
-    // changes at most once over a thread's whole query range: re-derived on change.
-    uint32_t drop_hi = 0xFFFFFFFFu, drop_k = 0u;
+    uint32_t drop_hi = 0xFFFFFFFFu, drop_k = 0u;  // dropout key cache (attn_keep32_t)
     uint32_t rs[32], rp[32];
     float vp[32], vd[32];
     for (int it = 0; it < niter; ++it) {
@@ -620,6 +643,8 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
         tmem_ld_wait();
         // element index of (query iq0, key jk); query iq0 + t is t * S elements further
         const uint64_t idx0 = (static_cast<uint64_t>(bh) * p.S + (i * 128 + col)) * p.S + jk;
+        float ks[32];
+        if (f.drop) attn_keep32_t(rng, p.S, idx0, lane, drop_hi, drop_k, ks);
 #pragma unroll
         for (int t = 0; t < 32; ++t) {
           const int iq = i * 128 + col + t;
@@ -627,18 +652,7 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tm_qkv,
           if (f.alibi) x += slope_l2 * static_cast<float>(jk - iq);
           float pr = ex2_approx(x - sLse[col + t]);
           if (f.causal && jk > iq) pr = 0.f;
-          float keep = 1.f;
-          if (f.drop) {
-            const uint64_t pair = (idx0 + static_cast<uint64_t>(t) * p.S) >> 1;
-            const uint32_t hi = static_cast<uint32_t>(pair >> 32);
-            if (hi != drop_hi) {
-              drop_hi = hi;
-              drop_k = drop_key(rng, hi);
-            }
-            const uint32_t bits = drop_bits_keyed(drop_k, static_cast<uint32_t>(pair));
-            const uint32_t u = (jk & 1) ? (bits >> 16) : (bits & 0xFFFFu);
-            keep = u >= rng.thr ? rng.inv_keep : 0.f;
-          }
+          const float keep = f.drop ? ks[t] : 1.f;
           vp[t] = pr * keep;
           vd[t] = (pr * p.scale) * (__uint_as_float(rp[t]) * keep - sDelta[col + t]);
         }

@@ -694,6 +694,12 @@ extern "C" int dtds_layernorm_bwd_blocks(int rows, int cols) {
   return blocks < cap ? (blocks < 1 ? 1 : blocks) : cap;
 }
 
+// 1 if dtds_layernorm_bwd uses separate kernels for dz and for dgamma/dbeta at this shape, i.e.
+// the two halves may be issued by two calls (dgamma = dbeta = NULL, then dz = NULL).
+extern "C" int dtds_layernorm_bwd_splittable(int rows, int cols) {
+  return (rows <= 64 * dtds::sm_count() && cols % 2 == 0) ? 1 : 0;
+}
+
 extern "C" int dtds_layernorm_bwd(const void* dy, const void* z, const float* mean,
                                   const float* rstd, const void* gamma, const void* dz_extra,
                                   void* dz, void* dx_drop, void* dgamma, void* dbeta,
@@ -704,7 +710,9 @@ extern "C" int dtds_layernorm_bwd(const void* dy, const void* z, const float* me
   if (rows <= 0) return 0;
   if (cols % 8 != 0) return -1;
   const int blocks = dtds_layernorm_bwd_blocks(rows, cols);
-  if (rows <= 64 * dtds::sm_count() && cols % 2 == 0) {
+  if (dtds_layernorm_bwd_splittable(rows, cols)) {
+    // dz == NULL: parameter gradients only (the caller runs them on another stream)
+    if (dz != nullptr)
     DTDS_HOST_CHECK(launch_pdl(
         ln_bwd_dx_kernel, dim3((rows + 7) / 8), dim3(256), 0, stream,
         static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(z), mean, rstd,
@@ -720,6 +728,10 @@ extern "C" int dtds_layernorm_bwd(const void* dy, const void* z, const float* me
                                  partial, blocks, cols, dgamma, dbeta, grads_fp32, accumulate));
     }
     return 0;
+  }
+  if (dz == nullptr) {
+    fprintf(stderr, "[dtds] layernorm_bwd: dz may only be NULL on the row-parallel path\n");
+    return -1;
   }
   const size_t smem = sizeof(float) * 2 * cols;
 #define DTDS_LN_BWD(VPL_)                                                                        \

@@ -308,6 +308,17 @@ class LayerNormFn(torch.autograd.Function):
         mg_g, acc_g = grad_target(gamma)
         mg_b, acc_b = grad_target(beta)
         direct = mg_g is not None and mg_b is not None and acc_g == acc_b
+        if direct and _WGRAD_SIDE and K.layernorm_bwd_splittable(z):
+            # dz feeds the next backward op; dgamma/dbeta feed nobody until the optimizer: they
+            # run on the weight-gradient side stream like the wgrad GEMMs.
+            dz, dxd, _, _ = K.layernorm_bwd(dy, z, mean, rstd, gamma, dz_extra=dskip, p_drop=ctx.p,
+                                            seed=ctx.seed, want_dx_drop=True, parts="dx")
+            with _OnSideStream(dy, z, mean, rstd, params=(gamma, beta)):
+                K.layernorm_bwd(dy, z, mean, rstd, gamma, dgamma_out=mg_g, dbeta_out=mg_b,
+                                accumulate=acc_g, parts="params")
+                grad_done(gamma)
+                grad_done(beta)
+            return dxd, (dz if ctx.has_res else None), None, None, None, None, None, None
         dz, dxd, dg, db = K.layernorm_bwd(
             dy, z, mean, rstd, gamma, dz_extra=dskip, p_drop=ctx.p, seed=ctx.seed,
             dgamma_out=mg_g if direct else None, dbeta_out=mg_b if direct else None,

@@ -170,12 +170,21 @@ def layernorm_fwd(x, residual, gamma, beta, eps, p_drop=0.0, seed=0, save_z=True
     return y, (z if need_z else x), mean, rstd
 
 
+def layernorm_bwd_splittable(z) -> bool:
+    """True if `layernorm_bwd` may be issued as parts="dx" and parts="params" on two streams."""
+    cols = z.shape[-1]
+    return bool(z.is_cuda and _lib.lib().dtds_layernorm_bwd_splittable(z.numel() // cols, cols))
+
+
 def layernorm_bwd(dy, z, mean, rstd, gamma, dz_extra=None, p_drop=0.0, seed=0, dgamma_out=None,
-                  dbeta_out=None, accumulate=False, want_dx_drop=False):
-    """Returns (dz, dx_drop, dgamma, dbeta).  dgamma/dbeta are written into *_out if given."""
+                  dbeta_out=None, accumulate=False, want_dx_drop=False, parts="all"):
+    """Returns (dz, dx_drop, dgamma, dbeta).  dgamma/dbeta are written into *_out if given.
+    parts="dx" skips the parameter gradients, parts="params" computes only them (both only where
+    `layernorm_bwd_splittable`)."""
     cols = z.shape[-1]
     rows = z.numel() // cols
     if not _lib.use_native(dy):
+        assert parts == "all"
         dz, dxd, dg, db = ref.layernorm_bwd(dy, z, mean, rstd, gamma, dz_extra, p_drop, seed)
         dz, dxd = dz.to(dy.dtype), dxd.to(dy.dtype)
         if dgamma_out is not None:
@@ -188,22 +197,25 @@ def layernorm_bwd(dy, z, mean, rstd, gamma, dz_extra=None, p_drop=0.0, seed=0, d
             dg, db = dg.to(gamma.dtype), db.to(gamma.dtype)
         return dz, (dxd if want_dx_drop else None), dg, db
     dy, z = _c(dy), _c(z)
-    dz = torch.empty_like(dy)
-    dxd = torch.empty_like(dy) if (want_dx_drop and p_drop > 0.0) else None
-    if dgamma_out is None:
+    want_dz, want_params = parts != "params", parts != "dx"
+    dz = torch.empty_like(dy) if want_dz else None
+    dxd = torch.empty_like(dy) if (want_dz and want_dx_drop and p_drop > 0.0) else None
+    if dgamma_out is None and want_params:
         dgamma_out = torch.empty_like(gamma)
         dbeta_out = torch.empty_like(gamma)
         accumulate = False
+    if not want_params:
+        dgamma_out = dbeta_out = None
     L = _lib.lib()
     blocks = L.dtds_layernorm_bwd_blocks(rows, cols)
-    partial = _scratch_f32(dy.device, blocks * 2 * cols, "ln_partial")
+    partial = _scratch_f32(dy.device, blocks * 2 * cols, f"ln_partial@{_lib.stream_ptr()}")  # per stream
     rc = L.dtds_layernorm_bwd(
         dy.data_ptr(), z.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
-        _lib.ptr(_c(dz_extra) if dz_extra is not None else None), dz.data_ptr(), _lib.ptr(dxd),
-        dgamma_out.data_ptr(), dbeta_out.data_ptr(), partial.data_ptr(), rows, cols, float(p_drop),
-        int(seed), _seed_ptr(), int(dgamma_out.dtype == torch.float32), int(accumulate),
-        _lib.stream_ptr())
-    _lib.check(rc, "dtds_layernorm_bwd")
+        _lib.ptr(_c(dz_extra) if dz_extra is not None else None), _lib.ptr(dz), _lib.ptr(dxd),
+        _lib.ptr(dgamma_out), _lib.ptr(dbeta_out), partial.data_ptr(), rows, cols, float(p_drop),
+        int(seed), _seed_ptr(), int(dgamma_out is not None and dgamma_out.dtype == torch.float32),
+        int(accumulate), _lib.stream_ptr())
+    _lib.check(rc, "dtds_layernorm_bwd", kernels={"all": 3, "dx": 1, "params": 2}[parts])
     if want_dx_drop and dxd is None:
         dxd = dz
     return dz, dxd, dgamma_out, dbeta_out

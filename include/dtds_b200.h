@@ -67,6 +67,9 @@ int dtds_layernorm_fwd(const void* x, const void* residual, const void* gamma, c
                        float eps, float p_drop, unsigned long long seed,
                        const unsigned long long* seed_dev, cudaStream_t stream);
 int dtds_layernorm_bwd_blocks(int rows, int cols); /* rows of `partial` the backward needs */
+/* 1 if dz and dgamma/dbeta come from separate kernels at this shape: the caller may then issue
+ * two calls (first with dgamma = dbeta = NULL, then with dz = NULL) on two streams. */
+int dtds_layernorm_bwd_splittable(int rows, int cols);
 int dtds_layernorm_bwd(const void* dy, const void* z, const float* mean, const float* rstd,
                        const void* gamma, const void* dz_extra, void* dz, void* dx_drop,
                        void* dgamma, void* dbeta, float* partial, int rows, int cols, float p_drop,
