@@ -152,37 +152,59 @@ def ddp_matches_single_process(rank, world, bucket_mb=0.05):
         ddp(ids, labels=labels).loss.backward()
 
 
-def ddp_training_loop(rank, world, use_graph=False):
-    """A few optimizer steps under DDP; all ranks must hold identical parameters afterwards."""
+def ddp_training_loop(rank, world, use_graph=False, fuse_opt=False):
+    """A few optimizer steps under DDP; all ranks must hold identical parameters afterwards.
+    fuse_opt: Adam runs per bucket on the communication stream right behind the bucket's
+    all-reduce (DistributedDataParallel.fuse_optimizer) and must give the same training curve."""
     from dtds_b200.optim import FusedAdam
     from dtds_b200.parallel.ddp import DistributedDataParallel
     dev = _dev(rank)
     dtype = torch.bfloat16 if dev.type == "cuda" else torch.float32
-    cfg, model = _tiny_bert(dev, dtype, seed=0, dropout=0.1)
-    ddp = DistributedDataParallel(model, bucket_cap_mb=0.1)
-    opt = FusedAdam(model.parameters(), lr=1e-3)
     g = torch.Generator().manual_seed(50 + rank)
-    ids = torch.randint(0, cfg.vocab_size, (2, 128), generator=g).to(dev)
-    labels = ids.clone()
+    ids, labels = None, None
 
-    def step(i, l):
-        opt.zero_grad()
-        loss = ddp(i, labels=l).loss
-        loss.backward()
-        opt.step()
-        return loss
+    def run(fused, graph, dropout):
+        nonlocal ids, labels
+        cfg, model = _tiny_bert(dev, dtype, seed=0, dropout=dropout)
+        ddp = DistributedDataParallel(model, bucket_cap_mb=0.1)
+        opt = FusedAdam(model.parameters(), lr=1e-3)
+        if fused:
+            ddp.fuse_optimizer(opt)
+        if ids is None:
+            ids = torch.randint(0, cfg.vocab_size, (2, 128), generator=g).to(dev)
+            labels = ids.clone()
 
-    if use_graph:
-        from dtds_b200.parallel.graph import GraphedStep
-        gs = GraphedStep(step, [ids, labels], warmup=2)
-        losses = [gs(ids, labels).item() for _ in range(6)]
-    else:
-        losses = [step(ids, labels).item() for _ in range(6)]
-    assert losses[-1] < losses[0], losses
-    flat = ddp.flat.param_flat.float()
-    other = flat.clone()
-    dist.broadcast(other, src=0)
-    assert torch.equal(flat, other), "replicas diverged"
+        def step(i, l):
+            opt.zero_grad()
+            loss = ddp(i, labels=l).loss
+            loss.backward()
+            opt.step()
+            return loss
+
+        if graph:
+            from dtds_b200.parallel.graph import GraphedStep
+            gs = GraphedStep(step, [ids, labels], warmup=2)
+            losses = [gs(ids, labels).item() for _ in range(6)]
+        else:
+            losses = [step(ids, labels).item() for _ in range(6)]
+        assert losses[-1] < losses[0], losses
+        flat = ddp.flat.param_flat.float()
+        other = flat.clone()
+        dist.broadcast(other, src=0)
+        assert torch.equal(flat, other), "replicas diverged"
+        return losses, flat
+
+    if not fuse_opt:
+        run(False, use_graph, 0.1)
+        return
+    # no dropout: the two runs see the same masks anyway, but keep the comparison free of RNG state
+    l_plain, w_plain = run(False, False, 0.0)
+    l_fused, w_fused = run(True, use_graph, 0.0)
+    if dev.type == "cpu":
+        assert torch.equal(w_plain, w_fused)
+    skip = 2 if use_graph else 0   # graph warm-up consumed two optimizer steps
+    for a, b in zip(l_fused, l_plain[skip:]):
+        assert abs(a - b) < 0.02 * max(1.0, abs(b)), (l_plain, l_fused)
 
 
 # --------------------------------------------------------------------------- ZeRO

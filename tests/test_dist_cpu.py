@@ -15,6 +15,10 @@ def test_ddp_training_loop_gloo():
     run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False,))
 
 
+def test_ddp_fused_optimizer_gloo():
+    run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False, True))
+
+
 def test_zero_stages_match_stage0_gloo():
     run_distributed("zero_stages_match_stage0", world=2, backend="gloo", timeout=600)
 

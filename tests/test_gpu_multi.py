@@ -30,6 +30,11 @@ def test_ddp_training_loop(use_graph):
     run_distributed("ddp_training_loop", world=2, backend="nccl", args=(use_graph,))
 
 
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_ddp_fused_optimizer(use_graph):
+    run_distributed("ddp_training_loop", world=2, backend="nccl", args=(use_graph, True))
+
+
 @pytest.mark.parametrize("arch", ["bloom-tiny", "bert-tiny"])
 def test_zero_stages_match_stage0(arch):
     run_distributed("zero_stages_match_stage0", world=2, backend="nccl", args=(arch,), timeout=600)
