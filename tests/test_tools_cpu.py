@@ -83,7 +83,9 @@ def test_launcher_env_contract_and_failure_propagation(tmp_path):
     script = tmp_path / "child.py"
     script.write_text("import os, sys\n"
                       "assert any(a.startswith('--local_rank=') for a in sys.argv)\n"
-                      "print('R', os.environ['RANK'], os.environ['LOCAL_RANK'], os.environ['WORLD_SIZE'], os.environ['MASTER_ADDR'])\n"
+                      # one write() per line: the two unbuffered children share the pipe
+                      "os.write(1, ('R %s %s %s %s\\n' % (os.environ['RANK'], os.environ['LOCAL_RANK'], "
+                      "os.environ['WORLD_SIZE'], os.environ['MASTER_ADDR'])).encode())\n"
                       "sys.exit(3 if os.environ['RANK'] == '1' and 'fail' in sys.argv else 0)\n")
     ok = _run("-m", "dtds_b200.launch", "--nproc-per-node", "2", str(script))
     assert ok.returncode == 0 and "R 0 0 2 127.0.0.1" in ok.stdout and "R 1 1 2 127.0.0.1" in ok.stdout
