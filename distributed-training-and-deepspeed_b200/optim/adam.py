@@ -141,6 +141,9 @@ class FusedAdam(torch.optim.Optimizer):
         b["pending"] -= 1
         if b["pending"] == 0:
             self.step_range(b["group"], b["lo"], b["hi"])
+        elif b["pending"] < 0:
+            raise RuntimeError("FusedAdam(overlap_with_backward=True): a second backward pass ran before "
+                               "zero_grad(); gradient accumulation needs overlap_with_backward=False")
 
     def _group_of(self, flat) -> "_FlatGroup":
         for g in self._groups:
