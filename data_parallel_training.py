@@ -99,15 +99,19 @@ def train(rank, world_size, batch_size, training_steps, bucket_size, model, back
     graphed = None
     training_start_time = time.time()
     progress_bar = tqdm(range(training_steps), disable=rank != 0)
-    for batch in train_dataloader:
+    from dtds_b200.utils.trace import annotate_model, nvtx_enabled, nvtx_range
+    if nvtx_enabled():   # DTDS_NVTX=1: per-step / per-layer / per-bucket ranges for a profiler timeline
+        annotate_model(net)
+    for step_idx, batch in enumerate(train_dataloader):
         input_ids, labels = batch["input_ids"], batch["labels"]
-        if use_graph and on_gpu and input_ids.shape[0] == batch_size:
-            if graphed is None:
-                from dtds_b200.parallel.graph import GraphedStep
-                graphed = GraphedStep(step_fn, [input_ids.to(device), labels.to(device)], warmup=2)
-            graphed(input_ids, labels)
-        else:
-            step_fn(input_ids.to(device, non_blocking=True), labels.to(device, non_blocking=True))
+        with nvtx_range(f"train step {step_idx}"):
+            if use_graph and on_gpu and input_ids.shape[0] == batch_size:
+                if graphed is None:
+                    from dtds_b200.parallel.graph import GraphedStep
+                    graphed = GraphedStep(step_fn, [input_ids.to(device), labels.to(device)], warmup=2)
+                graphed(input_ids, labels)
+            else:
+                step_fn(input_ids.to(device, non_blocking=True), labels.to(device, non_blocking=True))
         progress_bar.update(1)
     if on_gpu:
         torch.cuda.synchronize()

@@ -15,6 +15,7 @@ import torch
 
 from ..ops import kernels as K
 from ..parallel.flat import FlatBuffers, unique_params
+from ..utils.trace import nvtx_range
 
 
 class _FlatGroup:
@@ -203,6 +204,10 @@ class FusedAdam(torch.optim.Optimizer):
 
     @torch.no_grad()
     def step(self, closure=None):
+        with nvtx_range("FusedAdam.step"):
+            return self._step(closure)
+
+    def _step(self, closure=None):
         loss = closure() if closure is not None else None
         self._rebind()
         g0 = self.param_groups[0]

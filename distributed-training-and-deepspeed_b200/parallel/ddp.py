@@ -26,6 +26,7 @@ import torch.distributed as dist
 from torch import nn
 
 from .. import comm
+from ..utils.trace import nvtx_range
 from .flat import FlatBuffers
 
 
@@ -175,6 +176,10 @@ class DistributedDataParallel(nn.Module):
             self.optimizer.step_range(self.flat, b.lo, min(b.hi, self.flat.total), stream=stream)
 
     def _launch_bucket(self, b: _Bucket):
+        with nvtx_range(f"ddp.bucket{b.index} all_reduce {(b.hi - b.lo) * self.flat.grad_flat.element_size() >> 10} KiB"):
+            self._launch_bucket_impl(b)
+
+    def _launch_bucket_impl(self, b: _Bucket):
         b.launched = True
         g = self.flat.grad_flat
         esz = g.element_size()

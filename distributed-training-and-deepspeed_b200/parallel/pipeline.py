@@ -25,6 +25,8 @@ import torch
 import torch.distributed as dist
 from torch.utils.checkpoint import checkpoint as _checkpoint
 
+from ..utils import trace as _trace
+
 
 def split_sizes(n_items: int, n_groups: int) -> list[int]:
     """Group sizes of ``np.array_split(range(n_items), n_groups)``: the first ``n % k`` groups get
@@ -59,6 +61,8 @@ class IdleTracker:
         else:
             ev = time.perf_counter()
         self._open = (ev, label)
+        if _trace.nvtx_enabled():
+            _trace._push(label)
         if self.verbose:
             self.log(f"Entering {label} on device {self._dev_index()}")
 
@@ -73,6 +77,8 @@ class IdleTracker:
             end = time.perf_counter()
         self._segments.append((start, end, label))
         self._open = None
+        if _trace.nvtx_enabled():
+            _trace._pop()
         if self.verbose:
             self.log(f"Finished {label} on device {self._dev_index()}")
 

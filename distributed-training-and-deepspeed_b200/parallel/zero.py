@@ -37,6 +37,7 @@ from torch import nn
 
 from .. import comm
 from ..ops import kernels as K
+from ..utils.trace import nvtx_range
 from .flat import FlatBuffers
 
 
@@ -242,6 +243,10 @@ class ZeroEngine(nn.Module):
         return g["lr"], g["betas"][0], g["betas"][1], g["eps"], g["weight_decay"]
 
     def _launch_bucket(self, b: _ZBucket, overlap: bool):
+        with nvtx_range(f"zero{self.stage}.bucket{b.index} rs+adam+ag {b.hi - b.lo} elts"):
+            self._launch_bucket_impl(b, overlap)
+
+    def _launch_bucket_impl(self, b: _ZBucket, overlap: bool):
         """Reduce-scatter + Adam + all-gather for one bucket (stages 1-3)."""
         b.launched = True
         f = self.flat

@@ -3,3 +3,4 @@ wikitext-shaped datasets, memory telemetry, checkpointing."""
 from .devices import format_size, get_device, get_device_count  # noqa: F401
 from .data import SyntheticTextDataset, load_wikitext  # noqa: F401
 from .memory import memory_status  # noqa: F401
+from .trace import DeviceTimer, annotate_model, nvtx_range  # noqa: F401

@@ -133,3 +133,50 @@ def test_checkpoint_resume_matches_uninterrupted_run(tmp_path):
     assert first + rest == full
     sd = torch.load(tmp_path / "ck" / "model.pt")
     assert set(sd.keys()) == set(m1.state_dict().keys())
+
+
+def test_nvtx_ranges_are_balanced_and_free_when_off(monkeypatch):
+    """DTDS_NVTX ranges: nothing is emitted when off; when on, every push has its pop across the
+    model annotation, the DDP bucket launches and the optimizer step."""
+    from dtds_b200.models import build_model, get_config
+    from dtds_b200.optim import FusedAdam
+    from dtds_b200.parallel.ddp import DistributedDataParallel
+    from dtds_b200.utils import trace
+    events = []
+    monkeypatch.setattr(trace, "_push", lambda name: events.append(("push", name)))
+    monkeypatch.setattr(trace, "_pop", lambda: events.append(("pop", None)))
+    torch.manual_seed(0)
+    m = build_model(get_config("bert-tiny"))
+    ddp = DistributedDataParallel(m, bucket_cap_mb=0.1)
+    opt = FusedAdam(m.parameters(), lr=1e-3)
+    handles = trace.annotate_model(m)
+    ids = torch.randint(0, 100, (2, 128))
+
+    def step():
+        with trace.nvtx_range("train step"):
+            opt.zero_grad()
+            ddp(ids, labels=ids).loss.backward()
+            opt.step()
+
+    trace.set_nvtx(False)
+    step()
+    assert events == []
+    trace.set_nvtx(True)
+    try:
+        step()
+    finally:
+        trace.set_nvtx(False)
+        for h in handles:
+            h.remove()
+    depth = 0
+    for kind, _ in events:
+        depth += 1 if kind == "push" else -1
+        assert depth >= 0
+    assert depth == 0
+    names = [n for k, n in events if k == "push"]
+    assert names[0] == "train step" and "FusedAdam.step" in names
+    assert any(n.startswith("encoders.0 ") for n in names) and any(n.startswith("ddp.bucket") for n in names)
+    t = trace.DeviceTimer("cpu")
+    with t:
+        sum(range(1000))
+    assert t.count == 1 and t.ms(reduce=False) > 0

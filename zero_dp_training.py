@@ -88,6 +88,7 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
         model_engine.step()
         return loss
 
+    from dtds_b200.utils.trace import nvtx_range
     graphed = None
     use_graph = cuda_graph and on_gpu and stage < 3   # stage 3 re-points parameter storage per block
     steady_start, steady_from = None, 3
@@ -98,13 +99,14 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
             steady_start = time.time()
         input_ids = batch["input_ids"].to(device)
         labels = batch["labels"].to(device)
-        if use_graph and input_ids.shape[0] == batch_size:
-            if graphed is None:   # capture forward + backward + fused ZeRO step kernels once
-                from dtds_b200.parallel.graph import GraphedStep
-                graphed = GraphedStep(step_fn, [input_ids, labels], warmup=2)
-            loss = graphed(input_ids, labels)
-        else:
-            loss = step_fn(input_ids, labels)
+        with nvtx_range(f"train step {step_idx}"):
+            if use_graph and input_ids.shape[0] == batch_size:
+                if graphed is None:   # capture forward + backward + fused ZeRO step kernels once
+                    from dtds_b200.parallel.graph import GraphedStep
+                    graphed = GraphedStep(step_fn, [input_ids, labels], warmup=2)
+                loss = graphed(input_ids, labels)
+            else:
+                loss = step_fn(input_ids, labels)
         if rank == 0:
             if not quiet:
                 memory_status("Memory stats after training step:")
