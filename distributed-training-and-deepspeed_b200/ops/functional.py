@@ -13,6 +13,7 @@ pack or unpack copies ("DDP variant writes dW straight into th
 """
 from __future__ import annotations
 
+import os
 import itertools
 import math
 
@@ -72,7 +73,7 @@ def grad_done(param) -> None:
 # leaves idle.  The side stream is joined back at the end of backward (autograd engine callback);
 # gradient-ready callbacks fire inside the side-stream context, so the engines' events are
 # recorded on the stream that actually produced the gradient.
-_WGRAD_SIDE = __import__("os").environ.get("DTDS_WGRAD_STREAM", "1") != "0"
+_WGRAD_SIDE = os.environ.get("DTDS_WGRAD_STREAM", "1") != "0"
 _side_streams: dict = {}
 _join_queued: dict = {}
 
@@ -212,7 +213,7 @@ class LinearFn(torch.autograd.Function):
         return dx, dw, db, None, dres, None
 
 
-FUSE_SKIP_GRADS = __import__("os").environ.get("DTDS_FUSE_SKIP_GRADS", "1") != "0"
+FUSE_SKIP_GRADS = os.environ.get("DTDS_FUSE_SKIP_GRADS", "1") != "0"
 
 
 def _as2d(t, cols):

@@ -6,6 +6,7 @@ Shapes follow the C header ``include/dtds_b200.h``.
 """
 from __future__ import annotations
 
+import os
 import torch
 
 from . import _lib, reference as ref
@@ -97,7 +98,7 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
 
 
 _tune_cache: dict = {}
-_AUTOTUNE = __import__("os").environ.get("DTDS_AUTOTUNE", "1") != "0"
+_AUTOTUNE = os.environ.get("DTDS_AUTOTUNE", "1") != "0"
 
 
 def _tuned_block_n(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn, b_mn, act, out_fp32, alpha):
@@ -442,7 +443,7 @@ def cast(src, dst):
 
 
 # --------------------------------------------------------------------------------- attention
-_ATTN_TWO_STREAMS = __import__("os").environ.get("DTDS_ATTN_TWO_STREAMS", "1") != "0"
+_ATTN_TWO_STREAMS = os.environ.get("DTDS_ATTN_TWO_STREAMS", "1") != "0"
 _attn_streams: dict = {}
 
 
