@@ -24,6 +24,16 @@ def unique_params(params) -> list:
     return out
 
 
+def grad_uses(p) -> int:
+    """How many backward producers must report before `p`'s gradient-ready callback fires.  A
+    producer whose rows are handed to an engine sink (EmbeddingFn with `_sparse_sink`) does not
+    count: the engine folds those rows in itself."""
+    n = getattr(p, "_grad_uses", 1)
+    if getattr(p, "_sparse_sink", None) is not None:
+        n -= 1
+    return max(n, 1)
+
+
 class FlatBuffers:
     def __init__(self, params, *, param_dtype: torch.dtype | None = None,
                  grad_dtype: torch.dtype | None = None, device=None, align: int = 64,
@@ -87,7 +97,7 @@ class FlatBuffers:
                 p._numel = p.numel()
                 p._flat_offset = o
                 p._grad_written = False
-                p._uses_pending = getattr(p, "_grad_uses", 1)
+                p._uses_pending = grad_uses(p)
 
     # ------------------------------------------------------------------------------------
     def range_of(self, p) -> tuple[int, int]:
@@ -97,7 +107,7 @@ class FlatBuffers:
         """Start of a new backward pass: the first gradient write of each parameter overwrites."""
         for p in self.params:
             p._grad_written = False
-            p._uses_pending = getattr(p, "_grad_uses", 1)
+            p._uses_pending = grad_uses(p)
 
     def zero_unwritten_grads(self) -> None:
         """Parameters that received no gradient this step must not see last step's values."""

@@ -1,5 +1,7 @@
 """CPU / gloo world_size=2 plumbing tests (BASELINE.json config 1): process-group bootstrap,
 logged collectives, DDP bucket schedule and gradient equivalence, training loop."""
+import pytest
+
 from _mp import run_distributed
 
 
@@ -11,12 +13,17 @@ def test_ddp_matches_single_process_gloo():
     run_distributed("ddp_matches_single_process", world=2, backend="gloo")
 
 
+def test_ddp_sparse_embedding_rows_gloo():
+    run_distributed("ddp_matches_single_process", world=2, backend="gloo", args=(0.05, True))
+
+
 def test_ddp_training_loop_gloo():
     run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False,))
 
 
-def test_ddp_fused_optimizer_gloo():
-    run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False, True))
+@pytest.mark.parametrize("sparse", [False, True])
+def test_ddp_fused_optimizer_gloo(sparse):
+    run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False, True, sparse))
 
 
 def test_zero_stages_match_stage0_gloo():
