@@ -158,3 +158,71 @@ def test_gemm_throughput_report():
                      "cublas_ms": ms_ref, "cublas_tflops": fl / ms_ref / 1e9})
     _save(rows, "gemm_throughput.json")
     print(json.dumps(rows, indent=1))
+
+
+# ------------------------------------------------------------------------------------ split-K
+# csrc/gemm_splitk_sm100.cu was written after the round's GPU budget was spent: it compiles for
+# sm_100a (96 registers, no spills) but has not run on hardware yet, and nothing uses it unless
+# DTDS_SPLITK=1 or split_k is passed.  Opt in with DTDS_TEST_SPLITK=1.
+_splitk = pytest.mark.skipif(os.environ.get("DTDS_TEST_SPLITK", "0") == "0",
+                             reason="split-K GEMM not validated on hardware yet (set DTDS_TEST_SPLITK=1)")
+
+
+@_splitk
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm_splitk_layouts(a_mn, b_mn):
+    torch.manual_seed(0)
+    report, ok = [], True
+    for (M, N, Kd) in [(2048, 768, 3072), (2048, 768, 2304), (384, 200, 1032), (130, 136, 520), (768, 768, 2048)]:
+        for bn, s in K.splitk_candidates(K._lib.lib(), torch.device("cuda"), M, N, Kd):
+            a = _rand(Kd, M) if a_mn else _rand(M, Kd)
+            b = _rand(Kd, N) if b_mn else _rand(N, Kd)
+            want = ref.gemm(a, b, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32)
+            got = K.gemm(a, b, a_mn_major=a_mn, b_mn_major=b_mn, block_n=bn, split_k=s)
+            ok &= _check(f"{M}x{N}x{Kd} bn{bn} s{s}", got, want, Kd, report)
+            again = K.gemm(a, b, a_mn_major=a_mn, b_mn_major=b_mn, block_n=bn, split_k=s)   # counters were reset
+            ok &= bool(torch.equal(got, again))   # fixed summation order: bit-reproducible
+    _save(report, f"gemm_splitk_a{int(a_mn)}b{int(b_mn)}.json")
+    assert report and ok, [r for r in report if r["bad"] or r["nan"]][:4]
+
+
+@_splitk
+def test_gemm_splitk_epilogues():
+    torch.manual_seed(1)
+    M, N, Kd, bn, s = 2048, 768, 3072, 256, 3
+    report, ok = [], True
+    x, w = _rand(M, Kd, scale=0.5), _rand(N, Kd, scale=0.05)
+    bias, res = _rand(N), _rand(M, N)
+    pre = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    got = K.gemm(x, w, bias=bias, act=ref.ACT_GELU_ERF, residual=res, pre_out=pre, block_n=bn, split_k=s)
+    want, want_pre = ref.gemm(x, w, bias=bias, act=ref.ACT_GELU_ERF, residual=res, out_dtype=torch.float32,
+                              want_pre=True)
+    ok &= _check("bias+gelu+residual", got, want, Kd, report)
+    ok &= _check("pre_out", pre, want_pre, Kd, report)
+    # dgrad with the activation derivative fused (W consumed MN-major)
+    dy, u = _rand(M, Kd, scale=0.5), _rand(M, N)
+    wt = _rand(Kd, N, scale=0.05)
+    got = K.gemm(dy, wt, b_mn_major=True, act=ref.ACT_GELU_ERF, dact_in=u, block_n=bn, split_k=s)
+    want = ref.gemm(dy, wt, b_mn_major=True, act=ref.ACT_GELU_ERF, dact_in=u, out_dtype=torch.float32)
+    ok &= _check("dgrad*gelu'", got, want, Kd, report)
+    # wgrad accumulation into fp32
+    a, b2 = _rand(2048, 768), _rand(2048, 768)
+    acc = torch.randn(768, 768, device="cuda")
+    want = acc + ref.gemm(a, b2, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32)
+    K.gemm(a, b2, a_mn_major=True, b_mn_major=True, out=acc, accumulate=True, block_n=128, split_k=4)
+    ok &= _check("wgrad fp32 accumulate", acc, want, 2048, report, out_is_bf16=False)
+    _save(report, "gemm_splitk_epilogues.json")
+    assert ok, [r for r in report if r["bad"] or r["nan"]][:4]
+
+
+@_splitk
+def test_gemm_splitk_autotune_picks_a_valid_config(monkeypatch):
+    monkeypatch.setattr(K, "_SPLITK", True)
+    K._splitk_cache.clear()
+    x, w = _rand(2048, 3072), _rand(768, 3072, scale=0.05)
+    got = K.gemm(x, w)
+    want = ref.gemm(x, w, out_dtype=torch.float32)
+    report = []
+    assert _check("autotuned", got, want, 3072, report), report
+    (bn, s), = [v for k, v in K._splitk_cache.items() if k[:3] == (2048, 768, 3072)]
+    assert bn in (64, 128, 256) and s >= 1
