@@ -84,6 +84,8 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
     assert out.stride(-1) == 1 and out.shape == (M, N)
     out_fp32 = out.dtype == torch.float32
     L = _lib.lib()
+    if split_k >= 2 and block_n not in (128, 256):
+        block_n = 128   # the split-K kernel has 128- and 256-wide tiles only
     if block_n == 0 and ready_flags is None:
         block_n = _tuned_block_n(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn_major,
                                  b_mn_major, act, out_fp32, alpha)
@@ -93,7 +95,7 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
     if split_k >= 2:
         assert ready_flags is None and max_ctas == 0, "split-K excludes the all-gather mode and CTA caps"
         rc = _splitk_call(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn_major, b_mn_major,
-                          act, out_fp32, accumulate, alpha, block_n or 128, split_k)
+                          act, out_fp32, accumulate, alpha, block_n, split_k)
         _lib.check(rc, "dtds_gemm_bf16_splitk")
         return out
     rc = L.dtds_gemm_bf16_ex(
