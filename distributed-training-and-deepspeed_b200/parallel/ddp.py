@@ -247,10 +247,11 @@ class DistributedDataParallel(nn.Module):
                 packed[nb_rows:nb_rows + T * 8].copy_(ids1.reshape(-1).contiguous().view(torch.uint8))
                 ctx.all_gather(stage, 0, per, packed)
                 allb = stage.tensor(torch.uint8, per * self.world).view(self.world, per)
-                for r in range(self.world):
-                    r_rows = allb[r, :nb_rows].view(rows.dtype).view(1, T, H)
-                    r_ids = allb[r, nb_rows:nb_rows + T * 8].view(torch.int64).view(1, T)
-                    K.embedding_bwd(r_ids, r_rows, p.main_grad, None)
+                # same rows, same order, one writer per table row on every rank: replicas stay
+                # bit-identical (local atomics would round in a rank-dependent order)
+                g_rows = torch.stack([allb[r, :nb_rows].view(rows.dtype).view(T, H) for r in range(self.world)])
+                g_ids = torch.stack([allb[r, nb_rows:nb_rows + T * 8].view(torch.int64) for r in range(self.world)])
+                K.embedding_bwd_deterministic(g_ids, g_rows, p.main_grad)
                 b.sparse_pending = False
                 if b.deferred_step is not None:
                     self._step_bucket(b, self._comm_stream)
@@ -262,7 +263,7 @@ class DistributedDataParallel(nn.Module):
             all_ids = torch.empty(self.world, T, dtype=torch.int64, device=ids.device)
             comm.all_gather_into_tensor(all_rows, rows.contiguous(), group=self.group)
             comm.all_gather_into_tensor(all_ids, ids1.contiguous(), group=self.group)
-            K.embedding_bwd(all_ids, all_rows, p.main_grad, None)
+            K.embedding_bwd_deterministic(all_ids, all_rows, p.main_grad)
             b.sparse_pending = False
             if b.deferred_step is not None:
                 self._step_bucket(b, None)

@@ -4,7 +4,7 @@
 #   2 GPUs: sparse-row DDP mode (add --gpus 2 to gpurun and pass "multi" as the first argument)
 mkdir -p gpurun_out
 if [ "$1" = "multi" ]; then
-  DTDS_TEST_SPARSE_ROWS=1 python -m pytest tests/test_gpu_multi.py -x -q -k "sparse" 2>&1 | tail -30
+  DTDS_TEST_SPARSE_ROWS=1 python -m pytest tests/test_gpu_ops.py tests/test_gpu_multi.py -x -q -k "sparse or deterministic" 2>&1 | tail -30
   exit 0
 fi
 DTDS_TEST_SPLITK=1 python -m pytest tests/test_gpu_gemm.py -x -q -k splitk 2>&1 | tail -30
