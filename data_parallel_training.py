@@ -58,7 +58,7 @@ class _BlockRegressor(torch.nn.Module):
 
 
 def train(rank, world_size, batch_size, training_steps, bucket_size, model, backend, port, use_graph, seq_len,
-          overlap_optimizer=False):
+          overlap_optimizer=False, pretrained=None):
     from dtds_b200.models import build_model, get_config
     from dtds_b200.optim import HFAdamW
     from dtds_b200.parallel.ddp import DistributedDataParallel
@@ -75,7 +75,11 @@ def train(rank, world_size, batch_size, training_steps, bucket_size, model, back
         net = _BlockRegressor(vocab=cfg.vocab_size).to(device)
     else:
         cfg = get_config(MODEL_NAMES[model])
-        net = build_model(cfg).to(device=device, dtype=torch.bfloat16 if on_gpu else torch.float32)
+        net = build_model(cfg)
+        if pretrained:   # local HF BertForMaskedLM checkpoint (the reference downloads bert-*-cased)
+            from dtds_b200.models import load_pretrained
+            load_pretrained(net, pretrained)
+        net = net.to(device=device, dtype=torch.bfloat16 if on_gpu else torch.float32)
     tokenizer = synthetic_tokenizer(cfg)
     collator = synthetic_collator(tokenizer, mlm=True)
     optimizer = HFAdamW(net.parameters(), lr=5e-5)
@@ -134,6 +138,8 @@ if __name__ == "__main__":
     parser.add_argument("--seq-len", type=int, default=None)
     parser.add_argument("--cuda-graph", action="store_true")
     parser.add_argument("--overlap-optimizer", action="store_true")
+    parser.add_argument("--pretrained", type=str, default=None,
+                        help="local HF checkpoint (file or directory) to start from instead of random weights")
     args = parser.parse_args()
 
     backend = args.backend or ("nccl" if torch.cuda.is_available() else "gloo")
@@ -141,5 +147,5 @@ if __name__ == "__main__":
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     mp.spawn(train,
              args=(device_count, args.batch_size, args.training_steps, args.bucket_size, args.model, backend,
-                   args.port, args.cuda_graph, args.seq_len, args.overlap_optimizer),
+                   args.port, args.cuda_graph, args.seq_len, args.overlap_optimizer, args.pretrained),
              nprocs=device_count, join=True)

@@ -112,3 +112,141 @@ def count_parameters(model: nn.Module) -> int:
             seen.add(id(p))
             n += p.numel()
     return n
+
+
+# ------------------------------------------------------------------ HF parameter-name bridge
+# The reference trains HF checkpoints (AutoModelForCausalLM.from_pretrained("bigscience/bloom-560m"
+# / "facebook/opt-125m"), zero_dp_training.py:24).  These two functions map between HF's
+# BloomForCausalLM / OPTForCausalLM state dicts and this module's fused layout (one QKV weight with
+# columns Q | K | V, each heads x head_dim).
+_LEAVES = ("weight", "bias")
+
+
+def _bloom_qkv_from_hf(t: torch.Tensor, heads: int) -> torch.Tensor:
+    """HF BLOOM stores query_key_value per head: rows ordered [head, (q, k, v), head_dim]."""
+    d = t.shape[0] // (3 * heads)
+    rest = t.shape[1:]
+    return t.reshape(heads, 3, d, *rest).transpose(0, 1).reshape(3 * heads * d, *rest).contiguous()
+
+
+def _bloom_qkv_to_hf(t: torch.Tensor, heads: int) -> torch.Tensor:
+    d = t.shape[0] // (3 * heads)
+    rest = t.shape[1:]
+    return t.reshape(3, heads, d, *rest).transpose(0, 1).reshape(3 * heads * d, *rest).contiguous()
+
+
+def causal_lm_to_hf_state_dict(model: "CausalLM") -> dict:
+    """State dict with HF ``BloomForCausalLM`` / ``OPTForCausalLM`` key names."""
+    sd, cfg, out = model.state_dict(), model.cfg, {}
+    L, heads = cfg.num_hidden_layers, cfg.num_attention_heads
+    if cfg.arch == "bloom":
+        out["transformer.word_embeddings.weight"] = sd["word_embeddings"].clone()
+        for leaf in _LEAVES:
+            out[f"transformer.word_embeddings_layernorm.{leaf}"] = sd[f"embedding_ln.{leaf}"].clone()
+            out[f"transformer.ln_f.{leaf}"] = sd[f"final_ln.{leaf}"].clone()
+        names = {"input_ln": "input_layernorm", "attention.out": "self_attention.dense",
+                 "post_attention_ln": "post_attention_layernorm", "mlp.fc1": "mlp.dense_h_to_4h",
+                 "mlp.fc2": "mlp.dense_4h_to_h"}
+        for i in range(L):
+            for leaf in _LEAVES:
+                out[f"transformer.h.{i}.self_attention.query_key_value.{leaf}"] = \
+                    _bloom_qkv_to_hf(sd[f"layers.{i}.attention.qkv.{leaf}"], heads)
+                for mine, hf in names.items():
+                    out[f"transformer.h.{i}.{hf}.{leaf}"] = sd[f"layers.{i}.{mine}.{leaf}"].clone()
+        out["lm_head.weight"] = (sd["word_embeddings"] if model.lm_head_weight is None else sd["lm_head_weight"]).clone()
+        return out
+    if cfg.arch == "opt":
+        H = cfg.hidden_size
+        p = "model.decoder."
+        out[p + "embed_tokens.weight"] = sd["word_embeddings"].clone()
+        out[p + "embed_positions.weight"] = sd["position_embeddings"].clone()
+        for leaf in _LEAVES:
+            out[p + f"final_layer_norm.{leaf}"] = sd[f"final_ln.{leaf}"].clone()
+        names = {"input_ln": "self_attn_layer_norm", "attention.out": "self_attn.out_proj",
+                 "post_attention_ln": "final_layer_norm", "mlp.fc1": "fc1", "mlp.fc2": "fc2"}
+        for i in range(L):
+            for leaf in _LEAVES:
+                qkv = sd[f"layers.{i}.attention.qkv.{leaf}"]
+                for j, n in enumerate(("q_proj", "k_proj", "v_proj")):
+                    out[p + f"layers.{i}.self_attn.{n}.{leaf}"] = qkv[j * H:(j + 1) * H].clone()
+                for mine, hf in names.items():
+                    out[p + f"layers.{i}.{hf}.{leaf}"] = sd[f"layers.{i}.{mine}.{leaf}"].clone()
+        out["lm_head.weight"] = (sd["word_embeddings"] if model.lm_head_weight is None else sd["lm_head_weight"]).clone()
+        return out
+    raise ValueError(f"no HF bridge for arch {cfg.arch!r}")
+
+
+def causal_lm_from_hf_state_dict(model: "CausalLM", hf_sd: dict) -> "CausalLM":
+    """Loads a HF ``BloomForCausalLM`` / ``OPTForCausalLM`` state dict (e.g. a downloaded
+    bloom-560m / opt-125m checkpoint) into `model`, which must have been built from the matching
+    config."""
+    cfg, sd = model.cfg, {}
+    L, heads = cfg.num_hidden_layers, cfg.num_attention_heads
+    hf_sd = {k.removeprefix("module."): v for k, v in hf_sd.items()}
+    if cfg.arch == "bloom":
+        sd["word_embeddings"] = hf_sd["transformer.word_embeddings.weight"]
+        for leaf in _LEAVES:
+            sd[f"embedding_ln.{leaf}"] = hf_sd[f"transformer.word_embeddings_layernorm.{leaf}"]
+            sd[f"final_ln.{leaf}"] = hf_sd[f"transformer.ln_f.{leaf}"]
+        names = {"input_ln": "input_layernorm", "attention.out": "self_attention.dense",
+                 "post_attention_ln": "post_attention_layernorm", "mlp.fc1": "mlp.dense_h_to_4h",
+                 "mlp.fc2": "mlp.dense_4h_to_h"}
+        for i in range(L):
+            for leaf in _LEAVES:
+                sd[f"layers.{i}.attention.qkv.{leaf}"] = _bloom_qkv_from_hf(
+                    hf_sd[f"transformer.h.{i}.self_attention.query_key_value.{leaf}"], heads)
+                for mine, hf in names.items():
+                    sd[f"layers.{i}.{mine}.{leaf}"] = hf_sd[f"transformer.h.{i}.{hf}.{leaf}"]
+    elif cfg.arch == "opt":
+        p = "model.decoder."
+        sd["word_embeddings"] = hf_sd[p + "embed_tokens.weight"]
+        sd["position_embeddings"] = hf_sd[p + "embed_positions.weight"]
+        for leaf in _LEAVES:
+            sd[f"final_ln.{leaf}"] = hf_sd[p + f"final_layer_norm.{leaf}"]
+        names = {"input_ln": "self_attn_layer_norm", "attention.out": "self_attn.out_proj",
+                 "post_attention_ln": "final_layer_norm", "mlp.fc1": "fc1", "mlp.fc2": "fc2"}
+        for i in range(L):
+            for leaf in _LEAVES:
+                sd[f"layers.{i}.attention.qkv.{leaf}"] = torch.cat(
+                    [hf_sd[p + f"layers.{i}.self_attn.{n}.{leaf}"] for n in ("q_proj", "k_proj", "v_proj")], 0)
+                for mine, hf in names.items():
+                    sd[f"layers.{i}.{mine}.{leaf}"] = hf_sd[p + f"layers.{i}.{hf}.{leaf}"]
+    else:
+        raise ValueError(f"no HF bridge for arch {cfg.arch!r}")
+    if model.lm_head_weight is not None:
+        sd["lm_head_weight"] = hf_sd["lm_head.weight"]
+    own = model.state_dict()
+    missing = [k for k in own if k not in sd]
+    if missing:
+        raise KeyError(f"HF state dict lacks the sources of {missing[:4]}")
+    with torch.no_grad():
+        for k, v in own.items():
+            if v.shape != sd[k].shape:
+                raise ValueError(f"{k}: checkpoint shape {tuple(sd[k].shape)} != model shape {tuple(v.shape)}")
+            v.copy_(sd[k].to(dtype=v.dtype, device=v.device))
+    return model
+
+
+def load_pretrained(model: nn.Module, path: str) -> nn.Module:
+    """Loads a local HF checkpoint (a ``pytorch_model.bin`` / ``model.safetensors`` file, or a
+    directory holding one) into a model built by ``build_model``: the offline stand-in for the
+    reference's ``from_pretrained`` calls (data_parallel_training.py:30-31, zero_dp_training.py:24)."""
+    import os
+    if os.path.isdir(path):
+        for fname in ("model.safetensors", "pytorch_model.bin"):
+            if os.path.exists(os.path.join(path, fname)):
+                path = os.path.join(path, fname)
+                break
+        else:
+            raise FileNotFoundError(f"no model.safetensors / pytorch_model.bin under {path}")
+    if path.endswith(".safetensors"):
+        from safetensors.torch import load_file
+        sd = load_file(path)
+    else:
+        sd = torch.load(path, map_location="cpu", weights_only=True)
+    cfg = getattr(model, "cfg", None)
+    if cfg is not None and cfg.arch == "bert":
+        from .bert import from_hf_state_dict
+        from_hf_state_dict(model, sd)
+        return model
+    return causal_lm_from_hf_state_dict(model, sd)

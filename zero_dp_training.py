@@ -38,7 +38,7 @@ def resolve_config(model_name):
 
 
 def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_len=512, quiet=False,
-          cuda_graph=False):
+          cuda_graph=False, pretrained=None):
     from dtds_b200 import comm
     from dtds_b200.models import build_model
     from dtds_b200.parallel import zero
@@ -54,6 +54,9 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
     cfg = resolve_config(model_name)
     torch.manual_seed(0)
     model = build_model(cfg)
+    if pretrained:   # local HF checkpoint of the same architecture (the reference downloads it)
+        from dtds_b200.models import load_pretrained
+        load_pretrained(model, pretrained)
 
     ds_config = {
         "train_micro_batch_size_per_gpu": batch_size,
@@ -142,6 +145,9 @@ if __name__ == "__main__":
     parser.add_argument("--fp32", action="store_true", help="keep fp32 parameters (library collectives)")
     parser.add_argument("--quiet", action="store_true", help="no per-step MEMSTATS / progress bar")
     parser.add_argument("--cuda-graph", action="store_true", help="replay the step as one CUDA graph (stages 0-2)")
+    parser.add_argument("--pretrained", type=str, default=None,
+                        help="local HF checkpoint (file or directory) to start from instead of random weights")
     args, extra_args = parser.parse_known_args()
     train(args.model_name, args.batch_size, args.training_steps, args.stage, *extra_args,
-          bf16=False if args.fp32 else None, seq_len=args.seq_len, quiet=args.quiet, cuda_graph=args.cuda_graph)
+          bf16=False if args.fp32 else None, seq_len=args.seq_len, quiet=args.quiet, cuda_graph=args.cuda_graph,
+          pretrained=args.pretrained)
