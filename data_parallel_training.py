@@ -58,7 +58,7 @@ class _BlockRegressor(torch.nn.Module):
 
 
 def train(rank, world_size, batch_size, training_steps, bucket_size, model, backend, port, use_graph, seq_len,
-          overlap_optimizer=False, pretrained=None):
+          overlap_optimizer=False, pretrained=None, data=None):
     from dtds_b200.models import build_model, get_config
     from dtds_b200.optim import HFAdamW
     from dtds_b200.parallel.ddp import DistributedDataParallel
@@ -84,7 +84,8 @@ def train(rank, world_size, batch_size, training_steps, bucket_size, model, back
     collator = synthetic_collator(tokenizer, mlm=True)
     optimizer = HFAdamW(net.parameters(), lr=5e-5)
 
-    train_dataset = load_wikitext(tokenizer, collator, max_length=seq_len).select(range(batch_size * training_steps))
+    train_dataset = load_wikitext(tokenizer, collator, max_length=seq_len, path=data).select(
+        range(batch_size * training_steps))
     train_dataloader = DataLoader(train_dataset, batch_size=batch_size, shuffle=False,
                                   sampler=DistributedSampler(train_dataset), pin_memory=on_gpu)
 
@@ -138,6 +139,8 @@ if __name__ == "__main__":
     parser.add_argument("--seq-len", type=int, default=None)
     parser.add_argument("--cuda-graph", action="store_true")
     parser.add_argument("--overlap-optimizer", action="store_true")
+    parser.add_argument("--data", type=str, default=None,
+                        help="local text file, one passage per line (default: synthetic wikitext-shaped rows)")
     parser.add_argument("--pretrained", type=str, default=None,
                         help="local HF checkpoint (file or directory) to start from instead of random weights")
     args = parser.parse_args()
@@ -147,5 +150,5 @@ if __name__ == "__main__":
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     mp.spawn(train,
              args=(device_count, args.batch_size, args.training_steps, args.bucket_size, args.model, backend,
-                   args.port, args.cuda_graph, args.seq_len, args.overlap_optimizer, args.pretrained),
+                   args.port, args.cuda_graph, args.seq_len, args.overlap_optimizer, args.pretrained, args.data),
              nprocs=device_count, join=True)

@@ -77,9 +77,115 @@ def synthetic_collator(tokenizer, mlm: bool = True) -> _SyntheticCollator:
     return _SyntheticCollator(tokenizer, mlm)
 
 
-def load_wikitext(tokenizer, collator, max_length: int | None = None, num_rows: int = 36718, seed: int = 0):
+class WordHashTokenizer:
+    """Offline tokenizer for real text when no HF tokenizer files are on the machine: lower-cased
+    whitespace/punctuation split, each word hashed (FNV-1a) into ``[first_id, vocab_size)``.  Not
+    a language model's vocabulary, but deterministic, and it gives real token statistics (Zipfian
+    repeats, variable row lengths) to the kernels that care: embedding scatter-add, padding masks."""
+
+    def __init__(self, vocab_size: int, model_max_length: int = 512, mask_token_id: int = 103,
+                 pad_token_id: int = 0, first_id: int = 1000):
+        self.vocab_size, self.model_max_length = vocab_size, model_max_length
+        self.mask_token_id, self.pad_token_id = mask_token_id, pad_token_id
+        self.first_id = min(first_id, vocab_size // 2)
+
+    def encode(self, text: str) -> list:
+        import re
+        out, span = [], self.vocab_size - self.first_id
+        for w in re.findall(r"\w+|[^\w\s]", text.lower()):
+            h = 0xcbf29ce484222325
+            for ch in w.encode("utf-8"):
+                h = ((h ^ ch) * 0x100000001b3) & 0xFFFFFFFFFFFFFFFF
+            out.append(self.first_id + h % span)
+        return out
+
+
+class TextFileDataset(Dataset):
+    """Rows built the way the reference builds them from wikitext (util.py:40-53): one non-empty
+    line per row, truncated / padded to ``max_length``, masking applied ONCE at build time (static
+    masks); MLM rows follow the 15 % / 80-10-10 recipe of
+    ``DataCollatorForLanguageModeling``, causal rows use ``labels = input_ids``; padding is -100
+    in the labels.  `tokenizer` is a ``WordHashTokenizer`` or any object with ``encode(text)``
+    (e.g. a HF tokenizer loaded from local files)."""
+
+    def __init__(self, path: str, tokenizer, mlm: bool, max_length: int, mlm_probability: float = 0.15,
+                 seed: int = 0, limit: int | None = None):
+        g = torch.Generator().manual_seed(seed)
+        pad = getattr(tokenizer, "pad_token_id", 0) or 0
+        mask_id = getattr(tokenizer, "mask_token_id", 103)
+        vocab = getattr(tokenizer, "vocab_size", None) or len(tokenizer)
+        rows = []
+        with open(path, encoding="utf-8") as f:
+            for line in f:
+                line = line.strip()
+                if not line:
+                    continue
+                try:
+                    toks = tokenizer.encode(line, add_special_tokens=True)
+                except TypeError:
+                    toks = tokenizer.encode(line)
+                toks = list(toks)[:max_length]
+                if toks:
+                    rows.append(toks)
+                if limit is not None and len(rows) >= limit:
+                    break
+        if not rows:
+            raise ValueError(f"{path}: no non-empty lines")
+        ids = torch.full((len(rows), max_length), pad, dtype=torch.int64)
+        real = torch.zeros(len(rows), max_length, dtype=torch.bool)
+        for r, toks in enumerate(rows):
+            ids[r, :len(toks)] = torch.tensor(toks, dtype=torch.int64)
+            real[r, :len(toks)] = True
+        labels = ids.clone()
+        if mlm:
+            prob = torch.full(ids.shape, mlm_probability)
+            prob[~real] = 0.0
+            masked = torch.bernoulli(prob, generator=g).bool()
+            labels[~masked] = -100
+            replace = torch.bernoulli(torch.full(ids.shape, 0.8), generator=g).bool() & masked
+            ids[replace] = mask_id
+            rand = torch.bernoulli(torch.full(ids.shape, 0.5), generator=g).bool() & masked & ~replace
+            ids[rand] = torch.randint(0, vocab, (int(rand.sum()),), generator=g)
+        else:
+            labels[~real] = -100
+        self.input_ids, self.labels = ids, labels
+        self.attention_mask = real
+
+    def __len__(self):
+        return self.input_ids.shape[0]
+
+    def __getitem__(self, i):
+        return {"input_ids": self.input_ids[i], "labels": self.labels[i]}
+
+    def select(self, indices):
+        idx = torch.as_tensor(list(indices), dtype=torch.long)
+        if len(idx) and int(idx.max()) >= len(self):   # small files: wrap around like extra epochs
+            idx = idx % len(self)
+        out = object.__new__(TextFileDataset)
+        out.input_ids, out.labels = self.input_ids[idx], self.labels[idx]
+        out.attention_mask = self.attention_mask[idx]
+        return out
+
+
+def load_text_file(path: str, tokenizer, collator, max_length: int | None = None, seed: int = 0,
+                   limit: int | None = None):
+    """Real-text counterpart of `load_wikitext` for a local file with one passage per line (e.g.
+    an extracted ``wiki.train.raw``)."""
+    S = max_length or tokenizer.model_max_length
+    tok = tokenizer if hasattr(tokenizer, "encode") else WordHashTokenizer(
+        tokenizer.vocab_size, S, getattr(tokenizer, "mask_token_id", 103))
+    return TextFileDataset(path, tok, collator.mlm, S, getattr(collator, "mlm_probability", 0.15), seed, limit)
+
+
+def load_wikitext(tokenizer, collator, max_length: int | None = None, num_rows: int = 36718, seed: int = 0,
+                  path: str | None = None):
     """Same signature as the reference (util.py:38); 36,718 is the row count of the wikitext-2
-    train split.  Rows are generated lazily large enough for ``.select(range(n))``."""
+    train split.  Rows are generated lazily large enough for ``.select(range(n))``.  With `path`
+    (or ``DTDS_TEXT_FILE``) the rows come from that local text file instead of the generator."""
+    import os
+    path = path or os.environ.get("DTDS_TEXT_FILE")
+    if path:
+        return load_text_file(path, tokenizer, collator, max_length, seed)
     S = max_length or tokenizer.model_max_length
     return LazySyntheticDataset(num_rows, dict(seq_len=S, vocab_size=tokenizer.vocab_size, mlm=collator.mlm,
                                                seed=seed, mask_token_id=tokenizer.mask_token_id,

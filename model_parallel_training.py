@@ -55,7 +55,7 @@ def run(rank, device_count, args, backend):
     optimizer = AdamW(params, lr=5e-5, weight_decay=0.01) if params else None
 
     seq = args.seq_len or tokenizer.model_max_length
-    train_dataset = load_wikitext(tokenizer, collator, max_length=seq)
+    train_dataset = load_wikitext(tokenizer, collator, max_length=seq, path=args.data)
     generator = torch.Generator().manual_seed(1)   # same shuffle on every stage
     train_dataloader = DataLoader(train_dataset.select(range(args.batch_size * args.training_steps)),
                                   shuffle=True, batch_size=args.batch_size, generator=generator)
@@ -116,6 +116,8 @@ if __name__ == "__main__":
     parser.add_argument("--backend", choices=["nccl", "gloo"], default=None)
     parser.add_argument("--port", type=int, default=12356)
     parser.add_argument("--seq-len", type=int, default=None)
+    parser.add_argument("--data", type=str, default=None,
+                        help="local text file, one passage per line (default: synthetic wikitext-shaped rows)")
     args = parser.parse_args()
 
     backend = args.backend or ("nccl" if torch.cuda.is_available() else None)

@@ -180,3 +180,32 @@ def test_nvtx_ranges_are_balanced_and_free_when_off(monkeypatch):
     with t:
         sum(range(1000))
     assert t.count == 1 and t.ms(reduce=False) > 0
+
+
+def test_real_text_dataset_follows_the_reference_recipe(tmp_path):
+    """Local text file -> rows shaped like util.load_wikitext's: padded to max_length, static
+    15 % MLM masks on real tokens only, -100 elsewhere; causal rows copy input_ids."""
+    from dtds_b200.models import get_config
+    from dtds_b200.utils.data import load_wikitext, synthetic_collator, synthetic_tokenizer
+    text = tmp_path / "wiki.train.raw"
+    lines = ["", " = Valkyria Chronicles III = ", ""] + [
+        f"Passage {i} : " + " ".join(f"word{(i * 7 + j) % 50}" for j in range(20 + i % 30)) + " ." for i in range(200)]
+    text.write_text("\n".join(lines))
+    cfg = get_config("bert-tiny")
+    tok = synthetic_tokenizer(cfg)
+    mlm = load_wikitext(tok, synthetic_collator(tok, mlm=True), max_length=64, path=str(text))
+    assert len(mlm) == 201 and mlm[0]["input_ids"].shape == (64,)
+    ids, labels, real = mlm.input_ids, mlm.labels, mlm.attention_mask
+    assert (ids[~real] == 0).all() and (labels[~real] == -100).all()
+    frac = (labels[real] != -100).float().mean().item()
+    assert 0.11 < frac < 0.19, frac
+    picked = labels != -100
+    assert 0.7 < (ids[picked] == tok.mask_token_id).float().mean().item() < 0.9
+    assert ids.max().item() < cfg.vocab_size and ids[real & ~picked].min().item() >= 500
+    again = load_wikitext(tok, synthetic_collator(tok, mlm=True), max_length=64, path=str(text))
+    assert torch.equal(again.input_ids, ids)                      # static masks, deterministic
+    clm = load_wikitext(tok, synthetic_collator(tok, mlm=False), max_length=64, path=str(text))
+    assert torch.equal(clm.labels[clm.attention_mask], clm.input_ids[clm.attention_mask])
+    assert (clm.labels[~clm.attention_mask] == -100).all()
+    sub = mlm.select(range(300))                                   # more rows than lines: wraps
+    assert len(sub) == 300 and torch.equal(sub.input_ids[201], mlm.input_ids[0])

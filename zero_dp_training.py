@@ -38,7 +38,7 @@ def resolve_config(model_name):
 
 
 def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_len=512, quiet=False,
-          cuda_graph=False, pretrained=None):
+          cuda_graph=False, pretrained=None, data=None):
     from dtds_b200 import comm
     from dtds_b200.models import build_model
     from dtds_b200.parallel import zero
@@ -75,7 +75,8 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
     tokenizer = synthetic_tokenizer(cfg)
     collator = synthetic_collator(tokenizer, mlm=False)
     seq = min(seq_len, cfg.max_position_embeddings)
-    train_dataset = load_wikitext(tokenizer, collator, max_length=seq).select(range(batch_size * training_steps))
+    train_dataset = load_wikitext(tokenizer, collator, max_length=seq, path=data).select(
+        range(batch_size * training_steps))
     train_dataloader = DataLoader(train_dataset, batch_size=batch_size, shuffle=False,
                                   sampler=DistributedSampler(train_dataset, num_replicas=world_size,
                                                              rank=comm.get_rank()))
@@ -145,9 +146,11 @@ if __name__ == "__main__":
     parser.add_argument("--fp32", action="store_true", help="keep fp32 parameters (library collectives)")
     parser.add_argument("--quiet", action="store_true", help="no per-step MEMSTATS / progress bar")
     parser.add_argument("--cuda-graph", action="store_true", help="replay the step as one CUDA graph (stages 0-2)")
+    parser.add_argument("--data", type=str, default=None,
+                        help="local text file, one passage per line (default: synthetic wikitext-shaped rows)")
     parser.add_argument("--pretrained", type=str, default=None,
                         help="local HF checkpoint (file or directory) to start from instead of random weights")
     args, extra_args = parser.parse_known_args()
     train(args.model_name, args.batch_size, args.training_steps, args.stage, *extra_args,
           bf16=False if args.fp32 else None, seq_len=args.seq_len, quiet=args.quiet, cuda_graph=args.cuda_graph,
-          pretrained=args.pretrained)
+          pretrained=args.pretrained, data=args.data)
