@@ -1,1 +1,1 @@
-from .adam import AdamW, FusedAdam, HFAdamW  # noqa: F401
+from .adam import AdamW, FusedAdam, HFAdamW, clip_grad_norm_  # noqa: F401

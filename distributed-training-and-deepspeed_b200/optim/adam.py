@@ -293,3 +293,41 @@ def AdamW(params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, **kw
 def HFAdamW(params, lr=1e-3, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.0, **kw):
     """Defaults of the removed ``transformers.AdamW`` the DDP script used (eps 1e-6, wd 0)."""
     return FusedAdam(params, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, adam_w_mode=True, **kw)
+
+
+@torch.no_grad()
+def clip_grad_norm_(parameters, max_norm: float, eps: float = 1e-6) -> torch.Tensor:
+    """``torch.nn.utils.clip_grad_norm_`` for parameters whose gradients live in flat buffers
+    (``p.main_grad``; ``p.grad`` is None there, so torch's version would silently do nothing).
+    One norm and one scale per flat buffer instead of per tensor; parameters without a flat
+    gradient fall back to ``p.grad``.  Returns the total L2 norm before clipping.  Call it between
+    ``backward()`` and ``step()`` — not with ``overlap_with_backward`` / ``fuse_optimizer``, which
+    have already applied the update by then."""
+    if isinstance(parameters, torch.optim.Optimizer):
+        parameters = [p for g in parameters.param_groups for p in g["params"]]
+    params = unique_params(parameters)
+    flats, loose = {}, []
+    for p in params:
+        fo = getattr(p, "_flat_owner", None)
+        if fo is not None and fo.grad_flat is not None:
+            flats[id(fo)] = fo
+        elif p.grad is not None:
+            loose.append(p.grad)
+    sq = None
+    for fo in flats.values():
+        fo.absorb_autograd_grads()
+        fo.zero_unwritten_grads()
+        t = fo.grad_flat.float().pow(2).sum()
+        sq = t if sq is None else sq + t.to(sq.device)
+    for g in loose:
+        t = g.float().pow(2).sum()
+        sq = t if sq is None else sq + t.to(sq.device)
+    if sq is None:
+        return torch.zeros(())
+    total = sq.sqrt()
+    scale = (max_norm / (total + eps)).clamp(max=1.0)
+    for fo in flats.values():
+        fo.grad_flat.mul_(scale.to(fo.grad_flat.device).to(fo.grad_flat.dtype))
+    for g in loose:
+        g.mul_(scale.to(g.device).to(g.dtype))
+    return total

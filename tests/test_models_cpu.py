@@ -223,3 +223,25 @@ def test_load_pretrained_from_local_hf_checkpoint(tmp_path):
     with torch.no_grad():
         torch.testing.assert_close(mine(ids, return_logits=True).logits, hf(input_ids=ids).logits,
                                    rtol=1e-4, atol=1e-4)
+
+
+def test_clip_grad_norm_on_flat_gradients():
+    """Gradients written straight into the flat buffer (p.grad stays None) are clipped like
+    torch.nn.utils.clip_grad_norm_ clips ordinary ones."""
+    from dtds_b200.optim import FusedAdam, clip_grad_norm_
+    torch.manual_seed(0)
+    cfg = get_config("bert-tiny").replace(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0)
+    a = build_model(cfg)
+    b = build_model(cfg)
+    b.load_state_dict(a.state_dict())
+    ids = torch.randint(0, cfg.vocab_size, (2, 128))
+    opt = FusedAdam(a.parameters(), lr=1e-3)          # moves a's gradients into a flat buffer
+    opt.zero_grad()
+    a(ids, labels=ids).loss.backward()
+    b(ids, labels=ids).loss.backward()
+    assert all(p.grad is None for p in a.parameters())
+    want = torch.nn.utils.clip_grad_norm_(b.parameters(), 0.5)
+    got = clip_grad_norm_(opt, 0.5)
+    torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-6)
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        torch.testing.assert_close(pa.main_grad, pb.grad, rtol=1e-4, atol=1e-7)
