@@ -85,7 +85,16 @@ def custom_kernels_active(t: torch.Tensor | None = None) -> bool:
         return False
     if os.environ.get("DTDS_COMM", "custom").lower() == "nccl":
         return False
+    if spans_nodes():
+        return False   # peer-mapped memory / NVLS exist inside one NVSwitch domain only
     return torch.cuda.is_available() and (t is None or t.is_cuda)
+
+
+def spans_nodes() -> bool:
+    """True when the job has ranks on more than one box (launcher contract: LOCAL_WORLD_SIZE is the
+    number of ranks on this box; absent, e.g. under mp.spawn, the job is local)."""
+    local = os.environ.get("LOCAL_WORLD_SIZE")
+    return bool(local) and is_initialized() and get_world_size() > int(local)
 
 
 def symm_context(group=None):

@@ -52,8 +52,9 @@ class FlatBuffers:
             off += p.numel()
         self.used = off
         self.total = (off + pad_total_to - 1) // pad_total_to * pad_total_to
+        from .. import comm as _comm
         self.symmetric = symmetric and self.device.type == "cuda" and dist.is_initialized() \
-            and dist.get_world_size(group) > 1
+            and dist.get_world_size(group) > 1 and not _comm.spans_nodes()   # peer mapping is per box
         self.group = group
         self.param_buf = self.grad_buf = None  # SymmBuffer objects when symmetric
         esz_p = torch.empty((), dtype=self.param_dtype).element_size()

@@ -209,3 +209,57 @@ def test_real_text_dataset_follows_the_reference_recipe(tmp_path):
     assert (clm.labels[~clm.attention_mask] == -100).all()
     sub = mlm.select(range(300))                                   # more rows than lines: wraps
     assert len(sub) == 300 and torch.equal(sub.input_ids[201], mlm.input_ids[0])
+
+
+def test_launcher_multi_node_env_and_ssh_fanout(tmp_path):
+    """Two "nodes" on this machine: ranks are node_rank * slots + local_rank, every node sees the
+    same MASTER_ADDR/PORT, a gloo all-reduce crosses the nodes, and comm reports that the job spans
+    boxes (which keeps the engines off the peer-memory kernels).  The ssh fan-out is driven through
+    a stand-in for ssh that runs the remote command locally."""
+    child = tmp_path / "child.py"
+    child.write_text(
+        "import os, sys\n"
+        f"sys.path.insert(0, {ROOT!r})\n"
+        "import torch\n"
+        "from dtds_b200 import comm\n"
+        "comm.init_process_group(backend='gloo')\n"
+        "t = torch.tensor([float(comm.get_rank() + 1)])\n"
+        "comm.all_reduce(t)\n"
+        "os.write(1, ('R%s/%s local=%s/%s node=%s sum=%.0f spans=%s\\n' % (os.environ['RANK'], os.environ['WORLD_SIZE'],"
+        " os.environ['LOCAL_RANK'], os.environ['LOCAL_WORLD_SIZE'], os.environ['NODE_RANK'], t.item(),"
+        " comm.spans_nodes())).encode())\n"
+        "comm.destroy_process_group()\n")
+    fake_ssh = tmp_path / "fake_ssh.sh"
+    fake_ssh.write_text('#!/bin/sh\n# usage: fake_ssh.sh HOST COMMAND\nshift\nexec sh -c "$1"\n')
+    fake_ssh.chmod(0o755)
+    hostfile = tmp_path / "hostfile"
+    hostfile.write_text("127.0.0.1 slots=2\nlocalhost slots=2\n")
+    from dtds_b200.launch import free_port
+    r = _run("-m", "dtds_b200.launch", "--hostfile", str(hostfile), "--ssh", str(fake_ssh),
+             "--master-port", str(free_port()), "--no-local-rank", str(child))
+    assert r.returncode == 0, r.stdout + r.stderr
+    lines = sorted(l for l in r.stdout.splitlines() if l.startswith("R"))
+    assert lines == ["R0/4 local=0/2 node=0 sum=10 spans=True", "R1/4 local=1/2 node=0 sum=10 spans=True",
+                     "R2/4 local=0/2 node=1 sum=10 spans=True", "R3/4 local=1/2 node=1 sum=10 spans=True"], r.stdout
+
+
+def test_cluster_templates_render_hostfile_and_ssh_config():
+    """aws/cluster.py is the pure-Python half of the CDK stacks (the stacks themselves need
+    aws-cdk-lib): its hostfile is what the launcher parses."""
+    sys.path.insert(0, os.path.join(ROOT, "aws"))
+    try:
+        import cluster
+        import training_stack  # noqa: F401  (importable without aws-cdk-lib)
+    finally:
+        sys.path.pop(0)
+    from dtds_b200.launch import parse_hostfile
+    names = ["ec2-1.compute.amazonaws.com", "ec2-2.compute.amazonaws.com"]
+    hf = cluster.render_hostfile(names)
+    import tempfile
+    with tempfile.NamedTemporaryFile("w", suffix="hostfile", delete=False) as f:
+        f.write(hf)
+    assert parse_hostfile(f.name) == {names[0]: 8, names[1]: 8}
+    cfg = cluster.render_ssh_config(names, key_file="~/k.pem")
+    assert cfg.count("Host worker-") == 2 and "HostName ec2-2.compute.amazonaws.com" in cfg and "IdentityFile ~/k.pem" in cfg
+    spec = cluster.ClusterSpec(nodes=3)
+    assert spec.worker_names() == ["worker-1", "worker-2", "worker-3"] and spec.instance_type.startswith("p6-b200")
