@@ -45,7 +45,7 @@ def _parse_header(text: str):
     text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
     text = re.sub(r"//[^\n]*", " ", text)
     protos = {}
-    for m in re.finditer(r"\b(int|void|size_t|unsigned long long)\s+(dtds_\w+)\s*\(([^)]*)\)\s*;", text):
+    for m in re.finditer(r"\b(int|void|size_t|unsigned long long|long long)\s+(dtds_\w+)\s*\(([^)]*)\)\s*;", text):
         ret, name, args = m.group(1), m.group(2), m.group(3)
         argtypes = []
         for a in [x.strip() for x in args.split(",") if x.strip()]:
@@ -61,8 +61,13 @@ def _parse_header(text: str):
                 raise NativeLibraryError(f"unknown C type '{ty}' in prototype of {name}")
             argtypes.append(_CTYPES[ty])
         restype = {"int": ctypes.c_int, "void": None, "size_t": ctypes.c_size_t,
-                   "unsigned long long": ctypes.c_ulonglong}[ret]
+                   "unsigned long long": ctypes.c_ulonglong, "long long": ctypes.c_longlong}[ret]
         protos[name] = (restype, argtypes)
+    # a declaration this parser skipped would be called with ctypes' default int conversions
+    declared = set(re.findall(r"\b(dtds_\w+)\s*\(", text))
+    missed = declared - set(protos)
+    if missed:
+        raise NativeLibraryError(f"could not parse the prototype(s) of {sorted(missed)} in the C header")
     return protos
 
 

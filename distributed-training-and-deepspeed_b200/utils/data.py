@@ -89,15 +89,53 @@ class WordHashTokenizer:
         self.mask_token_id, self.pad_token_id = mask_token_id, pad_token_id
         self.first_id = min(first_id, vocab_size // 2)
 
+    # Byte-level rules, identical to csrc/text_rows.cpp (the native packer used for whole files):
+    # ASCII lower-casing; a word is a run of [a-z0-9_] or bytes >= 0x80; any other non-space byte
+    # is a token of its own.
     def encode(self, text: str) -> list:
-        import re
         out, span = [], self.vocab_size - self.first_id
-        for w in re.findall(r"\w+|[^\w\s]", text.lower()):
+        data = text.encode("utf-8")
+        i, n = 0, len(data)
+
+        def low(c):
+            return c + 32 if 65 <= c <= 90 else c
+
+        def is_word(c):
+            return 97 <= c <= 122 or 48 <= c <= 57 or c == 95 or c >= 0x80
+
+        while i < n:
+            c = low(data[i])
+            if c == 32 or 9 <= c <= 13:
+                i += 1
+                continue
             h = 0xcbf29ce484222325
-            for ch in w.encode("utf-8"):
-                h = ((h ^ ch) * 0x100000001b3) & 0xFFFFFFFFFFFFFFFF
+            if is_word(c):
+                while i < n and is_word(low(data[i])):
+                    h = ((h ^ low(data[i])) * 0x100000001b3) & 0xFFFFFFFFFFFFFFFF
+                    i += 1
+            else:
+                h = ((h ^ c) * 0x100000001b3) & 0xFFFFFFFFFFFFFFFF
+                i += 1
             out.append(self.first_id + h % span)
         return out
+
+    def encode_file(self, path: str, max_length: int, limit: int | None = None):
+        """(ids [rows, max_length] int64 padded, lengths [rows]) for the non-empty lines of `path`
+        through the multi-threaded native packer; None if the library is not built."""
+        try:
+            from ..ops import _lib
+            L = _lib.lib()
+        except Exception:  # noqa: BLE001
+            return None
+        import os
+        cap = limit if limit is not None else max(1, sum(1 for _ in open(path, "rb")))
+        ids = torch.empty(cap, max_length, dtype=torch.int64)
+        lens = torch.empty(cap, dtype=torch.int32)
+        rows = L.dtds_text_rows(os.fsencode(path), self.vocab_size, self.first_id, max_length, self.pad_token_id,
+                                ids.data_ptr(), lens.data_ptr(), cap, 0)
+        if rows < 0:
+            raise OSError(f"dtds_text_rows({path}) failed with code {rows}")
+        return ids[:rows], lens[:rows]
 
 
 class TextFileDataset(Dataset):
@@ -114,6 +152,14 @@ class TextFileDataset(Dataset):
         pad = getattr(tokenizer, "pad_token_id", 0) or 0
         mask_id = getattr(tokenizer, "mask_token_id", 103)
         vocab = getattr(tokenizer, "vocab_size", None) or len(tokenizer)
+        packed = tokenizer.encode_file(path, max_length, limit) if isinstance(tokenizer, WordHashTokenizer) else None
+        if packed is not None:   # native path: whole file tokenised and padded in C++
+            ids, lens = packed
+            if ids.shape[0] == 0:
+                raise ValueError(f"{path}: no non-empty lines")
+            real = torch.arange(max_length)[None, :] < lens[:, None]
+            self._finish(ids, real, mlm, mask_id, vocab, mlm_probability, g)
+            return
         rows = []
         with open(path, encoding="utf-8") as f:
             for line in f:
@@ -136,6 +182,9 @@ class TextFileDataset(Dataset):
         for r, toks in enumerate(rows):
             ids[r, :len(toks)] = torch.tensor(toks, dtype=torch.int64)
             real[r, :len(toks)] = True
+        self._finish(ids, real, mlm, mask_id, vocab, mlm_probability, g)
+
+    def _finish(self, ids, real, mlm, mask_id, vocab, mlm_probability, g):
         labels = ids.clone()
         if mlm:
             prob = torch.full(ids.shape, mlm_probability)

@@ -106,6 +106,13 @@ int dtds_mse(const void* x, const void* t, void* dx, float* loss, size_t n, floa
 /* ---- Embedding, cross-entropy, Adam (BertEmbeddings model/bert_mp.py:22; CrossEntropyLoss
  *      model_parallel_training.py:51,73; FusedAdam zero_dp_training.py:28-33; AdamW
  *      data_parallel_training.py:34, model_parallel_training.py:50) ------------------------- */
+/* Host-side (no GPU): non-empty lines of a text file -> int64 token rows [rows, max_len] with the
+ * word-hash vocabulary of utils/data.py (WordHashTokenizer), padded with pad_id; lengths[r] is the
+ * unpadded length.  Multi-threaded; returns rows written, -1 unreadable file, -2 bad arguments.
+ * Stands in for the Rust tokenizers + Arrow pipeline of the reference (util.py:47-51). */
+long long dtds_text_rows(const char* path, long long vocab, long long first_id, int max_len,
+                         long long pad_id, long long* ids, int* lengths, long long max_rows,
+                         int threads);
 int dtds_embedding_fwd(const long long* ids, const long long* type_ids, const void* word,
                        const void* pos, const void* type, void* out, int tokens, int seq,
                        int hidden, int pos_offset, int vocab, cudaStream_t stream);

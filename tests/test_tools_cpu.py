@@ -263,3 +263,23 @@ def test_cluster_templates_render_hostfile_and_ssh_config():
     assert cfg.count("Host worker-") == 2 and "HostName ec2-2.compute.amazonaws.com" in cfg and "IdentityFile ~/k.pem" in cfg
     spec = cluster.ClusterSpec(nodes=3)
     assert spec.worker_names() == ["worker-1", "worker-2", "worker-3"] and spec.instance_type.startswith("p6-b200")
+
+
+def test_native_text_packer_matches_python_tokenizer(tmp_path):
+    """csrc/text_rows.cpp (multi-threaded file -> padded token rows) against the Python statement
+    of the same byte-level rules, on text with punctuation, tabs, upper case and UTF-8."""
+    from dtds_b200.utils.data import WordHashTokenizer
+    tok = WordHashTokenizer(vocab_size=28996, model_max_length=48)
+    lines = ["Hello, World!  It's 2024 …", "", "\t  ", "naïve café — Ünïcödé_words and snake_case_9",
+             "x" * 300, "a b c " * 40] + [f"line {i}: The QUICK brown-fox (#{i}) jumps; over {i * 17} dogs." for i in range(600)]
+    path = tmp_path / "text.txt"
+    path.write_text("\n".join(lines), encoding="utf-8")
+    packed = tok.encode_file(str(path), 48)
+    assert packed is not None, "native library not built"
+    ids, lens = packed
+    want = [tok.encode(l)[:48] for l in lines if l.strip()]
+    assert ids.shape == (len(want), 48)
+    for r, w in enumerate(want):
+        assert lens[r].item() == len(w)
+        assert ids[r, :len(w)].tolist() == w and (ids[r, len(w):] == tok.pad_token_id).all()
+    assert ids.min().item() >= 0 and ids[ids != 0].min().item() >= tok.first_id and ids.max().item() < 28996
