@@ -7,8 +7,10 @@ The reference has no training checkpoints (only ``from_pretrained`` loads and a 
     (full fp32 tensors, consolidated from the master partitions for ZeRO 1-3), written by rank 0;
   * every rank writes ``optim_rank{r}.pt`` with its optimizer state (whole state for DDP /
     single-process, the owned partitions for ZeRO) and the step counter;
+  * layer-split / pipeline models (one process per stage) gather their stages' tensors into the
+    same single ``model.pt``; on load every stage picks the keys of the modules it owns;
   * ``load_checkpoint`` restores both, so a run resumed at step k continues bit-for-bit like
-    the uninterrupted one (tests/test_ckpt_cpu.py).
+    the uninterrupted one (tests/test_tools_cpu.py, tests/test_dist_cpu.py).
 """
 from __future__ import annotations
 
@@ -28,12 +30,34 @@ def _unwrap(model):
     return getattr(model, "module", model)
 
 
+def _stage_partitioned(model) -> bool:
+    """Layer-split / pipeline models driven by one process per stage hold only their own modules
+    (models/bert_mp.py: the others are placeholders), so a full state dict has to be gathered."""
+    m = _unwrap(model)
+    m = getattr(m, "bert", m)   # the pipeline adapter wraps the model
+    return bool(getattr(m, "distributed", False)) and hasattr(m, "group_ranges")
+
+
 def model_state_dict(model) -> dict:
-    """Full state dict on every rank (fp32 master values when an engine / fused optimizer has them)."""
+    """Full state dict on every rank (fp32 master values when an engine / fused optimizer has them;
+    gathered across stages for stage-partitioned models — a collective: every rank must call)."""
     if hasattr(model, "consolidated_fp32_state_dict"):
         return model.consolidated_fp32_state_dict()
-    return {k: v.detach().float().cpu() if v.is_floating_point() else v.detach().cpu()
-            for k, v in _unwrap(model).state_dict().items()}
+    target = _unwrap(model)
+    target = getattr(target, "bert", target) if _stage_partitioned(model) else target
+    local = {k: v.detach().float().cpu() if v.is_floating_point() else v.detach().cpu()
+             for k, v in target.state_dict().items()}
+    if _stage_partitioned(model):
+        parts = [None] * dist.get_world_size(target.group)
+        dist.all_gather_object(parts, local, group=target.group)
+        merged = {}
+        for part in parts:
+            overlap = set(part) & set(merged)
+            if overlap:
+                raise RuntimeError(f"stages report the same parameters: {sorted(overlap)[:4]}")
+            merged.update(part)
+        return merged
+    return local
 
 
 def save_checkpoint(path: str, model, optimizer=None, step: int = 0, extra: dict | None = None) -> None:
@@ -66,6 +90,13 @@ def load_checkpoint(path: str, model, optimizer=None, strict: bool = True) -> in
     meta = torch.load(os.path.join(path, "meta.pt"), map_location="cpu", weights_only=False)
     sd = torch.load(os.path.join(path, "model.pt"), map_location="cpu", weights_only=False)
     target = _unwrap(model)
+    if _stage_partitioned(model):
+        target = getattr(target, "bert", target)   # each stage loads the keys of its own modules
+        with torch.no_grad():
+            for k, v in target.state_dict().items():
+                if k not in sd:
+                    raise KeyError(f"checkpoint lacks {k}")
+                v.copy_(sd[k].to(v.dtype))
     if optimizer is not None and os.path.exists(os.path.join(path, f"optim_rank{rank}.pt")):
         osd = torch.load(os.path.join(path, f"optim_rank{rank}.pt"), map_location="cpu", weights_only=False)
         optimizer.load_state_dict(osd)   # restores fp32 masters and re-derives the working parameters

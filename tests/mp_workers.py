@@ -411,3 +411,59 @@ def zero_checkpoint_resume(rank, world, stage=2):
         sd = torch.load(os.path.join(path[0], "model.pt"))
         names = {n for n, _ in e3.module.named_parameters()}
         assert names <= set(sd.keys())
+
+
+def pipeline_checkpoint_resume(rank, world, chunks=2):
+    """One process per stage: the checkpoint's single model.pt holds every stage's tensors, and a
+    run resumed from it continues like the uninterrupted one."""
+    import os
+    import tempfile
+    from dtds_b200.models import get_config
+    from dtds_b200.models.bert_mp import BertModelWithMP
+    from dtds_b200.optim import AdamW
+    from dtds_b200.utils.ckpt import load_checkpoint, save_checkpoint
+    dev = _dev(rank)
+    dtype = torch.bfloat16 if dev.type == "cuda" else torch.float32
+    cfg = get_config("bert-tiny").replace(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0,
+                                          num_hidden_layers=4)
+    g = torch.Generator().manual_seed(7)
+    ids = torch.randint(0, cfg.vocab_size, (4, 128), generator=g)
+    labels = ids.clone()
+    labels[:, ::2] = -100
+
+    def make():
+        torch.manual_seed(0)
+        bert = BertModelWithMP(cfg, dtype=dtype)
+        pipe = bert.to_pipeline(chunks)
+        params = [p for p in bert.parameters()]
+        opt = AdamW(params, lr=1e-3) if params else None
+        return bert, pipe, opt
+
+    def steps(pipe, opt, n):
+        for _ in range(n):
+            pipe.forward_backward(ids, labels)
+            if opt is not None:
+                opt.step()
+                opt.zero_grad()
+
+    b1, p1, o1 = make()
+    steps(p1, o1, 4)
+    want = {k: v.detach().float().cpu().clone() for k, v in b1.state_dict().items()}
+    b2, p2, o2 = make()
+    steps(p2, o2, 2)
+    path = [tempfile.mkdtemp(prefix="dtds_pp_ckpt_") if rank == 0 else None]
+    dist.broadcast_object_list(path, src=0)
+    save_checkpoint(path[0], p2, o2, step=2)
+    b3, p3, o3 = make()
+    with torch.no_grad():   # make sure the load really restores something
+        for p in b3.parameters():
+            p.add_(1.0)
+    assert load_checkpoint(path[0], p3, o3) == 2
+    steps(p3, o3, 2)
+    for k, v in b3.state_dict().items():
+        assert torch.allclose(v.detach().float().cpu(), want[k], atol=1e-6 if dtype == torch.float32 else 3e-2), k
+    if rank == 0:
+        sd = torch.load(os.path.join(path[0], "model.pt"))
+        L = cfg.num_hidden_layers
+        assert any(k.startswith("embeddings.") for k in sd) and any(k.startswith("head.") for k in sd)
+        assert all(any(k.startswith(f"encoders.{i}.") for k in sd) for i in range(L)), sorted(sd)[:8]

@@ -37,3 +37,7 @@ def test_gpipe_matches_single_process_gloo():
 def test_zero_checkpoint_resume_gloo():
     run_distributed("zero_checkpoint_resume", world=2, backend="gloo", args=(2,), timeout=600)
     run_distributed("zero_checkpoint_resume", world=2, backend="gloo", args=(3,), timeout=600)
+
+
+def test_pipeline_checkpoint_resume_gloo():
+    run_distributed("pipeline_checkpoint_resume", world=2, backend="gloo", timeout=600)
