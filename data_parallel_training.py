@@ -58,7 +58,7 @@ class _BlockRegressor(torch.nn.Module):
 
 
 def train(rank, world_size, batch_size, training_steps, bucket_size, model, backend, port, use_graph, seq_len,
-          overlap_optimizer=False, pretrained=None, data=None):
+          overlap_optimizer=False, pretrained=None, data=None, save_dir=None, resume=None):
     from dtds_b200.models import build_model, get_config
     from dtds_b200.optim import HFAdamW
     from dtds_b200.parallel.ddp import DistributedDataParallel
@@ -101,6 +101,12 @@ def train(rank, world_size, batch_size, training_steps, bucket_size, model, back
         optimizer.step()
         return loss
 
+    start_step = 0
+    if resume:
+        from dtds_b200.utils.ckpt import load_checkpoint
+        start_step = load_checkpoint(resume, ddp, optimizer)
+        if rank == 0:
+            print(f"Resumed from {resume} at step {start_step}")
     graphed = None
     training_start_time = time.time()
     progress_bar = tqdm(range(training_steps), disable=rank != 0)
@@ -108,6 +114,8 @@ def train(rank, world_size, batch_size, training_steps, bucket_size, model, back
     if nvtx_enabled():   # DTDS_NVTX=1: per-step / per-layer / per-bucket ranges for a profiler timeline
         annotate_model(net)
     for step_idx, batch in enumerate(train_dataloader):
+        if step_idx < start_step:
+            continue   # rows the interrupted run already consumed
         input_ids, labels = batch["input_ids"], batch["labels"]
         with nvtx_range(f"train step {step_idx}"):
             if use_graph and on_gpu and input_ids.shape[0] == batch_size:
@@ -121,6 +129,9 @@ def train(rank, world_size, batch_size, training_steps, bucket_size, model, back
     if on_gpu:
         torch.cuda.synchronize()
     training_end_time = time.time()
+    if save_dir:
+        from dtds_b200.utils.ckpt import save_checkpoint
+        save_checkpoint(save_dir, ddp, optimizer, step=len(train_dataloader))
     print(f"\nTotal Training Time: {training_end_time - training_start_time:.2f} seconds")
     from dtds_b200 import comm
     comm.destroy_process_group()
@@ -139,6 +150,8 @@ if __name__ == "__main__":
     parser.add_argument("--seq-len", type=int, default=None)
     parser.add_argument("--cuda-graph", action="store_true")
     parser.add_argument("--overlap-optimizer", action="store_true")
+    parser.add_argument("--save-dir", type=str, default=None, help="write a checkpoint here after the last step")
+    parser.add_argument("--resume", type=str, default=None, help="checkpoint directory to continue from")
     parser.add_argument("--data", type=str, default=None,
                         help="local text file, one passage per line (default: synthetic wikitext-shaped rows)")
     parser.add_argument("--pretrained", type=str, default=None,
@@ -150,5 +163,6 @@ if __name__ == "__main__":
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     mp.spawn(train,
              args=(device_count, args.batch_size, args.training_steps, args.bucket_size, args.model, backend,
-                   args.port, args.cuda_graph, args.seq_len, args.overlap_optimizer, args.pretrained, args.data),
+                   args.port, args.cuda_graph, args.seq_len, args.overlap_optimizer, args.pretrained, args.data,
+                   args.save_dir, args.resume),
              nprocs=device_count, join=True)

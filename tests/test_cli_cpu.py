@@ -39,3 +39,25 @@ def test_model_parallel_script_pipeline_gloo_world2():
     out = r.stdout + r.stderr
     assert r.returncode == 0, out[-3000:]
     assert "Total Training Time:" in out and "Average Idle Time (ms)" in out
+
+
+def test_scripts_save_and_resume_with_real_text(tmp_path):
+    """--data (local text), --save-dir and --resume through the DDP and ZeRO entry points."""
+    text = tmp_path / "corpus.txt"
+    text.write_text("\n".join(f"Passage {i} about topic {i % 7} : " + " ".join(f"w{(i + j) % 40}" for j in range(30))
+                              for i in range(64)))
+    ck = tmp_path / "ddp_ckpt"
+    common = ["data_parallel_training.py", "--backend", "gloo", "--device-count", "2", "--model", "tiny",
+              "--batch-size", "2", "--seq-len", "64", "--data", str(text)]
+    r = _run(common + ["--training-steps", "4", "--port", "12431", "--save-dir", str(ck)])
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert sorted(os.listdir(ck)) == ["meta.pt", "model.pt", "optim_rank0.pt", "optim_rank1.pt"]
+    r = _run(common + ["--training-steps", "6", "--port", "12432", "--resume", str(ck)])
+    assert r.returncode == 0 and "Resumed from" in r.stdout and "at step 2" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    zk = tmp_path / "zero_ckpt"
+    zero = ["-m", "dtds_b200.launch", "--nproc-per-node", "2", "zero_dp_training.py", "--stage", "3", "--model-name",
+            "opt-tiny", "--seq-len", "64", "--quiet", "--data", str(text)]
+    r = _run(zero + ["--training-steps", "4", "--save-dir", str(zk)])
+    assert r.returncode == 0 and "Saved checkpoint" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+    r = _run(zero + ["--training-steps", "6", "--resume", str(zk)])
+    assert r.returncode == 0 and "Resumed from" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

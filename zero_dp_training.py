@@ -38,7 +38,7 @@ def resolve_config(model_name):
 
 
 def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_len=512, quiet=False,
-          cuda_graph=False, pretrained=None, data=None):
+          cuda_graph=False, pretrained=None, data=None, save_dir=None, resume=None):
     from dtds_b200 import comm
     from dtds_b200.models import build_model
     from dtds_b200.parallel import zero
@@ -93,10 +93,18 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
         return loss
 
     from dtds_b200.utils.trace import nvtx_range
+    start_step = 0
+    if resume:   # model.pt (consolidated fp32) + this rank's optimizer partition + step counter
+        from dtds_b200.utils.ckpt import load_checkpoint
+        start_step = load_checkpoint(resume, model_engine, optimizer)
+        if rank == 0:
+            print(f"Resumed from {resume} at step {start_step}")
     graphed = None
     use_graph = cuda_graph and on_gpu and stage < 3   # stage 3 re-points parameter storage per block
     steady_start, steady_from = None, 3
     for step_idx, batch in enumerate(train_dataloader):
+        if step_idx < start_step:
+            continue   # rows the interrupted run already consumed
         if step_idx == steady_from:
             if on_gpu:
                 torch.cuda.synchronize()
@@ -119,6 +127,11 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
     if on_gpu:
         torch.cuda.synchronize()
     training_end_time = time.time()
+    if save_dir:
+        from dtds_b200.utils.ckpt import save_checkpoint
+        save_checkpoint(save_dir, model_engine, optimizer, step=len(train_dataloader))
+        if rank == 0:
+            print(f"Saved checkpoint to {save_dir}")
     if rank == 0:
         print(f"\nTotal Training Time: {training_end_time - training_start_time:.2f} seconds")
         n_local = len(train_dataloader)
@@ -146,6 +159,8 @@ if __name__ == "__main__":
     parser.add_argument("--fp32", action="store_true", help="keep fp32 parameters (library collectives)")
     parser.add_argument("--quiet", action="store_true", help="no per-step MEMSTATS / progress bar")
     parser.add_argument("--cuda-graph", action="store_true", help="replay the step as one CUDA graph (stages 0-2)")
+    parser.add_argument("--save-dir", type=str, default=None, help="write a checkpoint here after the last step")
+    parser.add_argument("--resume", type=str, default=None, help="checkpoint directory to continue from")
     parser.add_argument("--data", type=str, default=None,
                         help="local text file, one passage per line (default: synthetic wikitext-shaped rows)")
     parser.add_argument("--pretrained", type=str, default=None,
@@ -153,4 +168,4 @@ if __name__ == "__main__":
     args, extra_args = parser.parse_known_args()
     train(args.model_name, args.batch_size, args.training_steps, args.stage, *extra_args,
           bf16=False if args.fp32 else None, seq_len=args.seq_len, quiet=args.quiet, cuda_graph=args.cuda_graph,
-          pretrained=args.pretrained, data=args.data)
+          pretrained=args.pretrained, data=args.data, save_dir=args.save_dir, resume=args.resume)
