@@ -208,7 +208,10 @@ class FusedAdam(torch.optim.Optimizer):
             return self._step(closure)
 
     def _step(self, closure=None):
-        loss = closure() if closure is not None else None
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():   # torch.optim convention: the closure recomputes loss + grads
+                loss = closure()
         self._rebind()
         g0 = self.param_groups[0]
         lr, (b1, b2), eps, wd = g0["lr"], g0["betas"], g0["eps"], g0["weight_decay"]
