@@ -31,19 +31,22 @@ namespace dtds {
 
 constexpr int kBM = 128;
 constexpr int kBK = 64;
-constexpr int kGemmThreads = 320;  // TMA warp + MMA warp + 8 epilogue warps
 constexpr int kFetchThreads = 128;  // + 4 fetch warps in the all-gather fused variant
 constexpr int kMaxFetchSegs = 16;
 
-template <int BN>
+// EPI = number of epilogue warps: 8 (two per TMEM lane quadrant, the profiled configuration) or 16
+// (four per quadrant: each warp drains a quarter of the tile's columns; costs one smem stage at
+// BN = 256 for the larger store-staging area).
+template <int BN, int EPI = 8>
 struct GemmCfg {
   static constexpr int kAStage = kBM * kBK * 2;
   static constexpr int kBStage = BN * kBK * 2;
   static constexpr int kStage = kAStage + kBStage;
-  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kStages = (BN == 256) ? (EPI == 16 ? 3 : 4) : (BN == 128 ? (EPI == 16 ? 5 : 6) : 8);
   static constexpr int kTmemCols = 2 * BN;  // two accumulator stages
-  static constexpr int kStageOut = 8 * 32 * 128;  // epilogue staging: 8 warps x 32 rows x 128 B
+  static constexpr int kStageOut = EPI * 32 * 128;  // epilogue staging: EPI warps x 32 rows x 128 B
   static constexpr int kSmemBytes = kStages * kStage + kStageOut + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kThreads = 64 + 32 * EPI;  // TMA warp + MMA warp + epilogue warps
 };
 
 struct GemmParams {
@@ -149,13 +152,13 @@ __device__ __forceinline__ void store_row32_f32(float* __restrict__ dst, int nva
   }
 }
 
-template <int BN, bool A_MN, bool B_MN, bool FETCH>
+template <int BN, bool A_MN, bool B_MN, bool FETCH, int EPI = 8>
 // 96 registers: 320 threads x 96 leaves room on the SM for a 512-thread, 64-register
 // communication block (overlapped gradient-bucket all-reduce) next to this persistent CTA.
 __global__ void __maxnreg__(96)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, EPI>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -188,7 +191,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 8);
+      mbar_init(&tmem_empty[s], EPI);
     }
     fence_mbar_init();
   }
@@ -282,12 +285,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (dbg != nullptr && it == 0) dbg[4] = clock64();  // all MMAs of the first tile issued
       }
     }
-  } else if (FETCH && warp >= 10) {
+  } else if (FETCH && warp >= 2 + EPI) {
     // ------------------------------------------------------------------ fetch warps (all-gather)
     // Chunk c of B (fetch_chunk bytes) is assembled by CTA (c mod grid): 128 threads stream it
     // from the owning ranks' shard buffers with 4 independent 128-bit peer loads in flight per
     // thread, then publish the chunk's arrival flag with release semantics.
-    const int ft = threadIdx.x - kGemmThreads;
+    const int ft = threadIdx.x - Cfg::kThreads;
     const unsigned long long nchunks = (p.fetch_total + p.fetch_chunk - 1) / p.fetch_chunk;
     for (unsigned long long c = blockIdx.x; c < nchunks; c += gridDim.x) {
       const unsigned long long b0 = c * p.fetch_chunk;
@@ -318,11 +321,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.fetch_flags + c), "r"(p.ready_epoch)
                      : "memory");
     }
-  } else if (warp >= 2 && warp < 10) {
+  } else if (warp >= 2 && warp < 2 + EPI) {
     // ------------------------------------------------------------------ epilogue warps
     const int q = warp & 3;          // TMEM lane quadrant this warp may access
     const int chalf = (warp - 2) >> 2;  // which half of the tile's column chunks this warp owns
-    constexpr int kChunksPerWarp = BN / 64;
+    constexpr int kChunksPerWarp = BN / (8 * EPI);  // 32-column chunks per warp (EPI/4 warps share a quadrant)
     constexpr int kGroup = kChunksPerWarp >= 2 ? 2 : 1;  // chunks staged together (64 or 32 columns)
     constexpr int kPieces = kGroup * 4;                   // 16-byte pieces per staged row
     uint8_t* stage = s_out + (warp - 2) * (32 * 128);
@@ -507,11 +510,11 @@ int sm_count() {
   return cached[dev];
 }
 
-template <int BN, bool A_MN, bool B_MN, bool FETCH = false>
+template <int BN, bool A_MN, bool B_MN, bool FETCH = false, int EPI = 8>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
                        int max_ctas, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, FETCH>;
+  using Cfg = GemmCfg<BN, EPI>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, FETCH, EPI>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -524,7 +527,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   int grid = sm_count();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (num_tiles < grid && !FETCH) grid = num_tiles;  // fetch mode keeps every SM pulling chunks
-  DTDS_HOST_CHECK(launch_pdl(kern, dim3(grid), dim3(kGemmThreads + (FETCH ? kFetchThreads : 0)),
+  DTDS_HOST_CHECK(launch_pdl(kern, dim3(grid), dim3(Cfg::kThreads + (FETCH ? kFetchThreads : 0)),
                              Cfg::kSmemBytes, stream, tmA, tmB, p));
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
@@ -565,6 +568,17 @@ static int pick_block_n(int M, int N, int K, int requested) {
 using namespace dtds;
 
 static long long* g_gemm_dbg = nullptr;
+// 16-warp epilogue variant (not yet run on hardware: opt-in through DTDS_GEMM_WIDE=1 or
+// dtds_gemm_set_wide_epilogue; BLOCK_N 128 / 256, not in all-gather mode).
+static int g_gemm_wide = [] {
+  const char* e = getenv("DTDS_GEMM_WIDE");
+  return e != nullptr && atoi(e) != 0 ? 1 : 0;
+}();
+extern "C" int dtds_gemm_set_wide_epilogue(int on) {
+  const int old = g_gemm_wide;
+  g_gemm_wide = on ? 1 : 0;
+  return old;
+}
 // Development aid: when set, every GEMM CTA writes 8 clock64() stamps (start, setup done, loads
 // issued, first operands landed, MMAs issued, accumulator ready, first tile stored, end) to
 // buf[blockIdx.x * 8 ...].  Pass NULL to switch it off.
@@ -637,6 +651,19 @@ static int gemm_impl(const void* A, const void* B, void* D, const void* bias, co
     p.flags_on_k = fetch->flags_on_k;
   }
   const bool f = fetch != nullptr;
+
+  if (g_gemm_wide && !f && bn >= 128) {
+#define DTDS_DISPATCH_WIDE(BN_)                                                                              \
+  if (bn == BN_) {                                                                                           \
+    if (!a_mn_major && !b_mn_major) return launch_gemm<BN_, false, false, false, 16>(tmA, tmB, p, max_ctas, stream); \
+    if (!a_mn_major && b_mn_major) return launch_gemm<BN_, false, true, false, 16>(tmA, tmB, p, max_ctas, stream);   \
+    if (a_mn_major && !b_mn_major) return launch_gemm<BN_, true, false, false, 16>(tmA, tmB, p, max_ctas, stream);   \
+    return launch_gemm<BN_, true, true, false, 16>(tmA, tmB, p, max_ctas, stream);                           \
+  }
+    DTDS_DISPATCH_WIDE(128)
+    DTDS_DISPATCH_WIDE(256)
+#undef DTDS_DISPATCH_WIDE
+  }
 
 #define DTDS_DISPATCH(BN_)                                                                          \
   if (bn == BN_) {                                                                                  \

@@ -110,6 +110,13 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
     return out
 
 
+def set_wide_epilogue(on: bool) -> bool:
+    """16-warp GEMM epilogue on/off (see dtds_gemm_set_wide_epilogue); returns the previous setting.
+    The BLOCK_N autotune cache is cleared because the ranking may change."""
+    _tune_cache.clear()
+    return bool(_lib.lib().dtds_gemm_set_wide_epilogue(int(bool(on))))
+
+
 # ---- split-K (csrc/gemm_splitk_sm100.cu): off unless DTDS_SPLITK=1 or split_k is passed ----------
 _SPLITK = os.environ.get("DTDS_SPLITK", "0") != "0"
 _splitk_bufs: dict = {}

@@ -31,6 +31,10 @@ extern "C" {
  * count and splits must not exceed K/64; `flags` holds one zeroed uint32 per tile
  * (dtds_gemm_splitk_tiles) and is left zeroed.  Launches that may overlap on the GPU need
  * separate workspaces.  The reference has no counterpart (cuBLAS picks its own split-K). */
+/* Switches dtds_gemm_bf16 / _ex between the 8-warp epilogue (default) and a 16-warp one (four
+ * warps per TMEM lane quadrant; BLOCK_N 128 / 256, not the all-gather mode).  Returns the previous
+ * setting.  Also set by DTDS_GEMM_WIDE=1 at load time. */
+int dtds_gemm_set_wide_epilogue(int on);
 int dtds_gemm_splitk_tiles(int M, int N, int block_n);
 size_t dtds_gemm_splitk_workspace_bytes(int M, int N, int block_n, int splits);
 int dtds_gemm_bf16_splitk(const void* A, const void* B, void* D, const void* bias,

@@ -7,7 +7,10 @@ if [ "$1" = "multi" ]; then
   DTDS_TEST_SPARSE_ROWS=1 python -m pytest tests/test_gpu_ops.py tests/test_gpu_multi.py -x -q -k "sparse or deterministic" 2>&1 | tail -30
   exit 0
 fi
-DTDS_TEST_SPLITK=1 python -m pytest tests/test_gpu_gemm.py -x -q -k splitk 2>&1 | tail -30
-for v in 0 1; do
-  DTDS_SPLITK=$v python bench.py --steps 20 --warmup 5 2>gpurun_out/splitk_$v.err | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('DTDS_SPLITK', $v, d['ms_per_step'], d['final_loss'])"
-done
+DTDS_TEST_SPLITK=1 DTDS_TEST_GEMM_WIDE=1 python -m pytest tests/test_gpu_gemm.py -q -k "splitk or wide" 2>&1 | tail -30
+show() { python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', d['ms_per_step'], d['final_loss'])"; }
+python bench.py --steps 20 --warmup 5 2>/dev/null | show baseline
+DTDS_SPLITK=1 python bench.py --steps 20 --warmup 5 2>gpurun_out/splitk.err | show DTDS_SPLITK=1
+DTDS_GEMM_WIDE=1 python bench.py --steps 20 --warmup 5 2>gpurun_out/wide.err | show DTDS_GEMM_WIDE=1
+python bench/gemm_shapes.py > gpurun_out/gemm_shapes_plain.txt; DTDS_GEMM_WIDE=1 python bench/gemm_shapes.py > gpurun_out/gemm_shapes_wide.txt
+paste gpurun_out/gemm_shapes_plain.txt gpurun_out/gemm_shapes_wide.txt | cut -c1-400

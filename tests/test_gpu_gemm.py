@@ -226,3 +226,39 @@ def test_gemm_splitk_autotune_picks_a_valid_config(monkeypatch):
     assert _check("autotuned", got, want, 3072, report), report
     (bn, s), = [v for k, v in K._splitk_cache.items() if k[:3] == (2048, 768, 3072)]
     assert bn in (64, 128, 256) and s >= 1
+
+
+# ------------------------------------------------------------------------------ wide epilogue
+_wide = pytest.mark.skipif(os.environ.get("DTDS_TEST_GEMM_WIDE", "0") == "0",
+                           reason="16-warp GEMM epilogue not validated on hardware yet (set DTDS_TEST_GEMM_WIDE=1)")
+
+
+@_wide
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+def test_gemm_wide_epilogue_layouts(a_mn, b_mn):
+    """Same kernel with 16 epilogue warps (template parameter): all layouts, ragged shapes, fused
+    epilogues, multi-tile CTAs (the TMEM double buffer hand-off counts 16 arrivals)."""
+    torch.manual_seed(0)
+    report, ok = [], True
+    old = K.set_wide_epilogue(True)
+    try:
+        for (M, N, Kd) in [(2048, 768, 768), (2048, 3072, 768), (4096, 4096, 512), (392, 328, 200), (130, 136, 72)]:
+            for bn in (128, 256):
+                if N < bn:
+                    continue
+                a = _rand(Kd, M) if a_mn else _rand(M, Kd)
+                b = _rand(Kd, N) if b_mn else _rand(N, Kd)
+                want = ref.gemm(a, b, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32)
+                got = K.gemm(a, b, a_mn_major=a_mn, b_mn_major=b_mn, block_n=bn)
+                ok &= _check(f"{M}x{N}x{Kd} bn{bn}", got, want, Kd, report)
+        if not a_mn and not b_mn:
+            x, w, bias, res = _rand(2048, 768, scale=0.5), _rand(3072, 768, scale=0.05), _rand(3072), _rand(2048, 3072)
+            pre = torch.empty(2048, 3072, dtype=torch.bfloat16, device="cuda")
+            got = K.gemm(x, w, bias=bias, act=ref.ACT_GELU_ERF, residual=res, pre_out=pre, block_n=256)
+            want, want_pre = ref.gemm(x, w, bias=bias, act=ref.ACT_GELU_ERF, residual=res, out_dtype=torch.float32,
+                                      want_pre=True)
+            ok &= _check("bias+gelu+residual", got, want, 768, report) and _check("pre_out", pre, want_pre, 768, report)
+    finally:
+        K.set_wide_epilogue(old)
+    _save(report, f"gemm_wide_a{int(a_mn)}b{int(b_mn)}.json")
+    assert report and ok, [r for r in report if r["bad"] or r["nan"]][:4]
