@@ -93,10 +93,33 @@ class ZeroOptimizer:
         self.engine.load_optimizer_state_dict(sd)
 
 
+def _reject_unsupported(config: dict) -> None:
+    """The reference's ds_config uses train_micro_batch_size_per_gpu, optimizer, comms_logger and
+    zero_optimization.{stage, reduce_bucket_size} (zero_dp_training.py:26-44).  DeepSpeed keys that
+    would change the training semantics but are not implemented here fail loudly instead of being
+    ignored."""
+    z = config.get("zero_optimization", {}) or {}
+    problems = []
+    if int(config.get("gradient_accumulation_steps", 1) or 1) != 1:
+        problems.append("gradient_accumulation_steps > 1")
+    if float(config.get("gradient_clipping", 0.0) or 0.0) != 0.0:
+        problems.append("gradient_clipping")
+    if (config.get("fp16") or {}).get("enabled", False):
+        problems.append("fp16 (use bf16)")
+    for key in ("offload_optimizer", "offload_param"):
+        if (z.get(key) or {}).get("device", "none") not in ("none", None):
+            problems.append(f"zero_optimization.{key}")
+    if (config.get("scheduler") or {}).get("type"):
+        problems.append("scheduler (step a torch scheduler on engine.optimizer instead)")
+    if problems:
+        raise NotImplementedError("ds_config keys not supported by dtds_b200.parallel.zero: " + ", ".join(problems))
+
+
 class ZeroEngine(nn.Module):
     def __init__(self, model: nn.Module, config: dict, model_parameters=None, process_group=None):
         super().__init__()
         self.config = config
+        _reject_unsupported(config)
         zcfg = config.get("zero_optimization", {}) or {}
         self.stage = int(zcfg.get("stage", 0))
         assert self.stage in (0, 1, 2, 3), f"invalid ZeRO stage {self.stage}"

@@ -245,3 +245,17 @@ def test_clip_grad_norm_on_flat_gradients():
     torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-6)
     for pa, pb in zip(a.parameters(), b.parameters()):
         torch.testing.assert_close(pa.main_grad, pb.grad, rtol=1e-4, atol=1e-7)
+
+
+def test_zero_engine_rejects_ds_config_keys_it_does_not_implement():
+    from dtds_b200.parallel import zero
+    m = build_model(get_config("bloom-tiny"))
+    base = {"train_micro_batch_size_per_gpu": 1, "optimizer": {"type": "Adam", "params": {"lr": 1e-3}},
+            "zero_optimization": {"stage": 0}}
+    for extra in ({"gradient_accumulation_steps": 4}, {"gradient_clipping": 1.0}, {"fp16": {"enabled": True}},
+                  {"zero_optimization": {"stage": 2, "offload_optimizer": {"device": "cpu"}}}):
+        with pytest.raises(NotImplementedError):
+            zero.initialize(model=m, model_parameters=m.parameters(), config={**base, **extra})
+    eng, opt, _, _ = zero.initialize(model=m, model_parameters=m.parameters(),
+                                     config={**base, "gradient_accumulation_steps": 1, "gradient_clipping": 0.0})
+    assert eng.zero_optimization_stage() == 0
