@@ -58,7 +58,7 @@ class _BlockRegressor(torch.nn.Module):
 
 
 def train(rank, world_size, batch_size, training_steps, bucket_size, model, backend, port, use_graph, seq_len,
-          overlap_optimizer=False, pretrained=None, data=None, save_dir=None, resume=None):
+          overlap_optimizer=False, pretrained=None, data=None, save_dir=None, resume=None, json_out=None):
     from dtds_b200.models import build_model, get_config
     from dtds_b200.optim import HFAdamW
     from dtds_b200.parallel.ddp import DistributedDataParallel
@@ -113,9 +113,14 @@ def train(rank, world_size, batch_size, training_steps, bucket_size, model, back
     from dtds_b200.utils.trace import annotate_model, nvtx_enabled, nvtx_range
     if nvtx_enabled():   # DTDS_NVTX=1: per-step / per-layer / per-bucket ranges for a profiler timeline
         annotate_model(net)
+    steady_start, steady_from = None, start_step + 3   # set-up, autotuning, graph capture are over by then
     for step_idx, batch in enumerate(train_dataloader):
         if step_idx < start_step:
             continue   # rows the interrupted run already consumed
+        if step_idx == steady_from:
+            if on_gpu:
+                torch.cuda.synchronize()
+            steady_start = time.time()
         input_ids, labels = batch["input_ids"], batch["labels"]
         with nvtx_range(f"train step {step_idx}"):
             if use_graph and on_gpu and input_ids.shape[0] == batch_size:
@@ -133,6 +138,18 @@ def train(rank, world_size, batch_size, training_steps, bucket_size, model, back
         from dtds_b200.utils.ckpt import save_checkpoint
         save_checkpoint(save_dir, ddp, optimizer, step=len(train_dataloader))
     print(f"\nTotal Training Time: {training_end_time - training_start_time:.2f} seconds")
+    n_local = len(train_dataloader)
+    if rank == 0 and steady_start is not None and n_local > steady_from:
+        dt = (training_end_time - steady_start) / (n_local - steady_from)
+        line = {"ms_per_step": round(dt * 1e3, 3), "samples_per_s": round(batch_size * world_size / dt, 1),
+                "ranks": world_size, "steps_timed": n_local - steady_from}
+        print(f"Steady state (local steps {steady_from + 1}..{n_local}): {line['ms_per_step']:.2f} ms/step, "
+              f"{line['samples_per_s']:.1f} samples/s over {world_size} rank(s)")
+        if json_out:
+            import json
+            with open(json_out, "w") as f:
+                json.dump({"script": "data_parallel_training.py", "model": model, "batch_size": batch_size,
+                           "cuda_graph": bool(use_graph), **line}, f)
     from dtds_b200 import comm
     comm.destroy_process_group()
 
@@ -150,6 +167,7 @@ if __name__ == "__main__":
     parser.add_argument("--seq-len", type=int, default=None)
     parser.add_argument("--cuda-graph", action="store_true")
     parser.add_argument("--overlap-optimizer", action="store_true")
+    parser.add_argument("--json-out", type=str, default=None, help="write the steady-state throughput here (rank 0)")
     parser.add_argument("--save-dir", type=str, default=None, help="write a checkpoint here after the last step")
     parser.add_argument("--resume", type=str, default=None, help="checkpoint directory to continue from")
     parser.add_argument("--data", type=str, default=None,
@@ -164,5 +182,5 @@ if __name__ == "__main__":
     mp.spawn(train,
              args=(device_count, args.batch_size, args.training_steps, args.bucket_size, args.model, backend,
                    args.port, args.cuda_graph, args.seq_len, args.overlap_optimizer, args.pretrained, args.data,
-                   args.save_dir, args.resume),
+                   args.save_dir, args.resume, args.json_out),
              nprocs=device_count, join=True)
