@@ -14,3 +14,4 @@ DTDS_SPLITK=1 python bench.py --steps 20 --warmup 5 2>gpurun_out/splitk.err | sh
 DTDS_GEMM_WIDE=1 python bench.py --steps 20 --warmup 5 2>gpurun_out/wide.err | show DTDS_GEMM_WIDE=1
 python bench/gemm_shapes.py > gpurun_out/gemm_shapes_plain.txt; DTDS_GEMM_WIDE=1 python bench/gemm_shapes.py > gpurun_out/gemm_shapes_wide.txt
 paste gpurun_out/gemm_shapes_plain.txt gpurun_out/gemm_shapes_wide.txt | cut -c1-400
+python bench/kernels_roofline.py | tee gpurun_out/kernels_roofline.txt   # copy the JSON to profiles/ afterwards
