@@ -28,6 +28,8 @@ def _entry(rank, world, backend, port, fn_name, args, errq):
         from dtds_b200 import comm
         if backend == "nccl":
             torch.cuda.set_device(rank)
+        else:   # CPU ranks share the machine's cores instead of each spawning one thread per core
+            torch.set_num_threads(max(1, (os.cpu_count() or 2) // world))
         comm.init_process_group(backend=backend, rank=rank, world_size=world)
         import mp_workers
         getattr(mp_workers, fn_name)(rank, world, *args)

@@ -12,6 +12,7 @@ def _run(args, timeout=600, env=None):
     e = dict(os.environ)
     e.update(env or {})
     e["CUDA_VISIBLE_DEVICES"] = e.get("CUDA_VISIBLE_DEVICES", "")
+    e.setdefault("OMP_NUM_THREADS", str(max(1, (os.cpu_count() or 2) // 2)))   # two ranks share the cores
     return subprocess.run([sys.executable, *args], cwd=ROOT, capture_output=True, text=True, timeout=timeout, env=e)
 
 
