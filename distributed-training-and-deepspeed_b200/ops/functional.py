@@ -375,7 +375,29 @@ def attention(qkv, B, S, heads, *, scale=None, causal=False, key_bias=None, alib
     H = qkv.shape[-1] // 3
     if scale is None:
         scale = 1.0 / math.sqrt(H // heads)
+    if qkv.is_cuda and S % 128 != 0:
+        # the tcgen05 kernels work on 128-row blocks: other lengths run padded, with the extra keys
+        # masked out and the extra query rows dropped
+        return attention_padded(qkv, B, S, heads, scale=scale, causal=causal, key_bias=key_bias, alibi=alibi,
+                                p_drop=p_drop, training=training)
     return AttentionFn.apply(qkv, B, S, heads, scale, causal, key_bias, alibi, p_drop, training)
+
+
+def attention_padded(qkv, B, S, heads, *, scale, causal=False, key_bias=None, alibi=None, p_drop=0.0,
+                     training=False, multiple: int = 128):
+    """Attention for a sequence length that is not a multiple of the kernels' 128-row block: pads
+    Q/K/V rows with zeros up to the next multiple, gives the padded keys a -1e9 bias (exp
+    underflows to exactly 0) and returns the first S rows.  Padding and slicing are ordinary
+    autograd ops around the fused function, so the backward needs nothing extra."""
+    Sp = (S + multiple - 1) // multiple * multiple
+    H3 = qkv.shape[-1]
+    padded = torch.nn.functional.pad(qkv.reshape(B, S, H3), (0, 0, 0, Sp - S)).reshape(B * Sp, H3)
+    kb = torch.zeros(B, Sp, dtype=torch.float32, device=qkv.device)
+    kb[:, S:] = -1e9
+    if key_bias is not None:
+        kb[:, :S] = key_bias.to(torch.float32)
+    out = AttentionFn.apply(padded, B, Sp, heads, scale, causal, kb, alibi, p_drop, training)
+    return out.reshape(B, Sp, H3 // 3)[:, :S].reshape(B * S, H3 // 3)
 
 
 # --------------------------------------------------------------------------------- embedding

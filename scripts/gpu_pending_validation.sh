@@ -7,7 +7,7 @@ if [ "$1" = "multi" ]; then
   DTDS_TEST_SPARSE_ROWS=1 python -m pytest tests/test_gpu_ops.py tests/test_gpu_multi.py -x -q -k "sparse or deterministic" 2>&1 | tail -30
   exit 0
 fi
-DTDS_TEST_SPLITK=1 DTDS_TEST_GEMM_WIDE=1 python -m pytest tests/test_gpu_gemm.py -q -k "splitk or wide" 2>&1 | tail -30
+DTDS_TEST_SPLITK=1 DTDS_TEST_GEMM_WIDE=1 DTDS_TEST_PENDING=1 python -m pytest tests/test_gpu_gemm.py tests/test_gpu_attention.py -q -k "splitk or wide or not_multiple" 2>&1 | tail -30
 show() { python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', d['ms_per_step'], d['final_loss'])"; }
 python bench.py --steps 20 --warmup 5 2>/dev/null | show baseline
 DTDS_SPLITK=1 python bench.py --steps 20 --warmup 5 2>gpurun_out/splitk.err | show DTDS_SPLITK=1

@@ -106,3 +106,26 @@ def test_attention_throughput_report():
     with open(os.path.join(OUT_DIR, "attn_throughput.json"), "w") as f:
         json.dump(rep, f)
     print(rep)
+
+
+@pytest.mark.skipif(__import__("os").environ.get("DTDS_TEST_PENDING", "0") == "0",
+                    reason="padding wrapper added after the GPU budget was spent (set DTDS_TEST_PENDING=1)")
+@pytest.mark.parametrize("S", [100, 200, 333])
+def test_attention_sequence_length_not_multiple_of_128(S):
+    """Fn.attention pads to the kernels' 128-row block (masked keys, dropped query rows)."""
+    import math
+    from dtds_b200.ops import functional as Fn
+    from dtds_b200.ops import reference as ref
+    torch.manual_seed(0)
+    B, heads, d = 2, 4, 64
+    qkv = (torch.randn(B * S, 3 * heads * d, device="cuda") * 0.5).to(torch.bfloat16).requires_grad_(True)
+    out = Fn.attention(qkv, B, S, heads, causal=True)
+    g = torch.randn_like(out)
+    (out.float() * g.float()).sum().backward()
+    q32 = qkv.detach().float().cpu().requires_grad_(True)
+    q, k, v = (t.reshape(B, S, heads, d).transpose(1, 2) for t in q32.split(heads * d, dim=-1))
+    want, _ = ref.attention(q, k, v, scale=1 / math.sqrt(d), causal=True)
+    want = want.transpose(1, 2).reshape(B * S, heads * d)
+    (want * g.float().cpu()).sum().backward()
+    assert (out.float().cpu() - want).abs().max().item() < 3e-2
+    assert (qkv.grad.float().cpu() - q32.grad).abs().max().item() < 6e-2 * max(1.0, q32.grad.abs().max().item())

@@ -107,3 +107,23 @@ def test_gemm_epilogues_and_activation_derivatives():
         torch.testing.assert_close(ref.act_grad(x.detach(), act), x.grad, rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(ref.gemm(a.t().contiguous(), b.t().contiguous(), a_mn_major=True, b_mn_major=True),
                                a @ b.t(), rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_attention_padded_to_block_multiple_matches_unpadded(causal):
+    """Sequence lengths that are not a multiple of 128 run padded on the GPU kernels; the padding
+    wrapper (pure autograd ops around the fused function) must not change values or gradients."""
+    from dtds_b200.ops import functional as Fn
+    torch.manual_seed(5)
+    B, S, heads, d = 2, 100, 2, 64
+    qkv = torch.randn(B * S, 3 * heads * d, requires_grad=True)
+    kb = torch.zeros(B, S)
+    kb[0, -9:] = -1e9
+    want = Fn.AttentionFn.apply(qkv, B, S, heads, 0.125, causal, kb, None, 0.0, False)
+    g = torch.randn_like(want)
+    (want * g).sum().backward()
+    gw, qkv.grad = qkv.grad.clone(), None
+    got = Fn.attention_padded(qkv, B, S, heads, scale=0.125, causal=causal, key_bias=kb)
+    (got * g).sum().backward()
+    torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(qkv.grad, gw, rtol=1e-4, atol=1e-6)
