@@ -25,7 +25,6 @@ import torch
 import torch.distributed as dist
 from torch import nn
 
-from ..ops import functional as Fn
 from ..parallel.pipeline import IdleTracker, PipelineStage, split_ranges
 from .bert import BertEmbeddings, BertLayer, BertOnlyMLMHead
 from .config import ModelConfig

@@ -8,7 +8,6 @@ falling back to PyTorch ops (CPU-only machines use the reference implementations
 from __future__ import annotations
 
 import ctypes
-import os
 import re
 import threading
 from pathlib import Path

@@ -32,7 +32,6 @@ from __future__ import annotations
 import os
 
 import torch
-import torch.distributed as dist
 from torch import nn
 
 from .. import comm
