@@ -8,7 +8,7 @@ bf16 compute with fp32 master weights, synthetic MLM token batches, random-init 
     python bench.py --gpus 1 --steps 20 --warmup 5
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
         --master-port 29511 bench.py --gpus 8 --steps 20 --warmup 5
-    python bench.py --impl reference ...      # the unmodified reference (unavailable offline)
+    python bench.py --impl reference ...      # the unmodified reference script (baseline/_ref), fp32
     python bench.py --impl torch ...          # stand-in baseline: HF BERT + torch DDP + AdamW
 
 Prints ONE JSON line (rank 0).  `value` is device-timed (CUDA events, max over ranks) over exactly
@@ -96,24 +96,22 @@ class ClockSampler:
 
 
 def reference_arm(args):
-    """The unmodified reference lives (if it could be installed) under baseline/_ref.  It has no
-    setup.py/pyproject.toml, imports transformers.AdamW (removed) and downloads bert-base-cased and
-    wikitext from the hub at start-up, so it cannot run in this offline image; see DESIGN.md."""
-    ref_dir = os.path.join(ROOT, "baseline", "_ref")
-    why = None
-    if not os.path.isdir(ref_dir) or not os.listdir(ref_dir):
-        why = ("reference not installable: /root/reference has no setup.py/pyproject.toml "
-               "(pip: 'neither setup.py nor pyproject.toml found'); its script also needs the removed "
-               "transformers.AdamW and hub downloads (no network)")
-    else:
-        sys.path.insert(0, ref_dir)
-        try:
-            import data_parallel_training  # noqa: F401
-            why = "reference imported but requires hub downloads of bert-base-cased and wikitext (no network)"
-        except Exception as e:  # noqa: BLE001
-            why = f"reference import failed: {type(e).__name__}: {str(e)[:120]}"
-    if int(os.environ.get("RANK", "0")) == 0:
-        print(json.dumps({"impl": "reference", "unavailable": why}))
+    """Runs the unmodified reference (baseline/_ref, see baseline/run_reference.py and DESIGN.md §4).
+    Under torchrun only rank 0 starts it: the reference spawns its own N workers with mp.spawn."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
+    sys.path.insert(0, os.path.join(ROOT, "baseline"))
+    try:
+        import run_reference
+        local = int(os.environ.get("LOCAL_RANK", "0"))
+        out = run_reference.run(args.gpus, args.steps, args.warmup, batch=args.batch_size,
+                                model="large" if args.model == "large" else "base", bucket_mb=args.bucket_size,
+                                clock_sampler=ClockSampler(local))
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        out = {"impl": "reference", "unavailable": f"{type(e).__name__}: {e}; "
+               + traceback.format_exc(limit=4).strip().replace("\n", " | ")[-800:]}
+    print(json.dumps(out), flush=True)
     return 0
 
 
