@@ -34,15 +34,16 @@ constexpr int kBK = 64;
 constexpr int kFetchThreads = 128;  // + 4 fetch warps in the all-gather fused variant
 constexpr int kMaxFetchSegs = 16;
 
-// EPI = number of epilogue warps: 8 (two per TMEM lane quadrant, the profiled configuration) or 16
-// (four per quadrant: each warp drains a quarter of the tile's columns; costs one smem stage at
-// BN = 256 for the larger store-staging area).
-template <int BN, int EPI = 8>
+// CG = 1: one CTA per 128 x BN tile.  CG = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) per
+// 256 x BN tile; each CTA stages its own 128 rows of A and BN/2 rows of B, so the pair moves half
+// of the B bytes per output element, which is what bounds the main loop (L2 -> shared memory fill).
+template <int BN, int CG = 1>
 struct GemmCfg {
+  static constexpr int EPI = 8;  // epilogue warps: two per TMEM lane quadrant
   static constexpr int kAStage = kBM * kBK * 2;
-  static constexpr int kBStage = BN * kBK * 2;
+  static constexpr int kBStage = (BN / CG) * kBK * 2;
   static constexpr int kStage = kAStage + kBStage;
-  static constexpr int kStages = (BN == 256) ? (EPI == 16 ? 3 : 4) : (BN == 128 ? (EPI == 16 ? 5 : 6) : 8);
+  static constexpr int kStages = CG == 2 ? (BN == 256 ? 6 : 8) : ((BN == 256) ? 4 : (BN == 128 ? 6 : 8));
   static constexpr int kTmemCols = 2 * BN;  // two accumulator stages
   static constexpr int kStageOut = EPI * 32 * 128;  // epilogue staging: EPI warps x 32 rows x 128 B
   static constexpr int kSmemBytes = kStages * kStage + kStageOut + 1024 /*align slack*/ + 256 /*barriers*/;
@@ -152,13 +153,15 @@ __device__ __forceinline__ void store_row32_f32(float* __restrict__ dst, int nva
   }
 }
 
-template <int BN, bool A_MN, bool B_MN, bool FETCH, int EPI = 8>
+template <int BN, bool A_MN, bool B_MN, bool FETCH, int CG = 1>
 // 96 registers: 320 threads x 96 leaves room on the SM for a 512-thread, 64-register
 // communication block (overlapped gradient-bucket all-reduce) next to this persistent CTA.
 __global__ void __maxnreg__(96)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmParams p) {
-  using Cfg = GemmCfg<BN, EPI>;
+  using Cfg = GemmCfg<BN, CG>;
+  constexpr int EPI = Cfg::EPI;
+  static_assert(!(FETCH && CG == 2), "the all-gather fused mode runs single-CTA tiles");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -174,10 +177,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  // CTA pair: rank 0 (leader) owns the `full` and `tmem_empty` barriers and issues the MMAs.
+  const uint32_t crank = CG == 2 ? cluster_ctarank() : 0u;
+  const int unit = CG == 2 ? (blockIdx.x >> 1) : blockIdx.x;       // persistent tile walker id
+  const int nunits = CG == 2 ? (gridDim.x >> 1) : gridDim.x;
   long long* dbg = p.dbg != nullptr ? p.dbg + static_cast<size_t>(blockIdx.x) * 16 : nullptr;
   if (dbg != nullptr && threadIdx.x == 0) dbg[0] = clock64();
 
-  const int num_m = (p.M + kBM - 1) / kBM;
+  const int num_m = (p.M + kBM * CG - 1) / (kBM * CG);
   const int num_n = (p.N + BN - 1) / BN;
   const int num_tiles = num_m * num_n;
   const int num_kb = (p.K + kBK - 1) / kBK;
@@ -191,16 +198,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], EPI);
+      mbar_init(&tmem_empty[s], EPI * CG);
     }
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, Cfg::kTmemCols);
-    tmem_relinquish();
+    if constexpr (CG == 2) {
+      tmem_alloc_pair(tmem_slot, Cfg::kTmemCols);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(tmem_slot, Cfg::kTmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_trigger();
@@ -212,9 +224,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (lane == 0) {
       int s = 0;
       uint32_t ph = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile % num_m) * kBM;
+      for (int tile = unit; tile < num_tiles; tile += nunits) {
+        const int m0 = (tile % num_m) * (kBM * CG) + static_cast<int>(crank) * kBM;
         const int n0 = (tile / num_m) * BN;
+        const int nb0 = n0 + static_cast<int>(crank) * (BN / CG);   // first B row this CTA stages
         if (p.ready_flags != nullptr && !p.flags_on_k) {
           // All-gather fused mode: B rows [n0, n0+BN) are written by fetch warps (of any CTA of
           // this grid, or by an earlier kernel); wait for the arrival flag(s) covering them, then
@@ -229,22 +242,42 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                              p.ready_epoch);
           }
           mbar_wait(&empty[s], ph ^ 1);
-          mbar_expect_tx(&full[s], Cfg::kStage);
           uint8_t* a_dst = sA + s * Cfg::kAStage;
           uint8_t* b_dst = sB + s * Cfg::kBStage;
-          if constexpr (!A_MN) {
-            tma_load_2d(a_dst, &tmA, &full[s], kb * kBK, m0, kEvictNormal);
-          } else {
+          if constexpr (CG == 2) {
+            // Both CTAs' bytes are counted on the leader's barrier: the MMA needs both halves.
+            if (crank == 0) mbar_expect_tx(&full[s], 2 * Cfg::kStage);
+            const uint32_t fb = mapa_u32(smem_u32(&full[s]), 0);
+            if constexpr (!A_MN) {
+              tma_load_2d_pair(a_dst, &tmA, fb, kb * kBK, m0, kEvictNormal);
+            } else {
 #pragma unroll
-            for (int j = 0; j < kBM / 64; ++j)
-              tma_load_2d(a_dst + j * 8192, &tmA, &full[s], m0 + j * 64, kb * kBK, kEvictNormal);
-          }
-          if constexpr (!B_MN) {
-            tma_load_2d(b_dst, &tmB, &full[s], kb * kBK, n0, kEvictNormal);
-          } else {
+              for (int j = 0; j < kBM / 64; ++j)
+                tma_load_2d_pair(a_dst + j * 8192, &tmA, fb, m0 + j * 64, kb * kBK, kEvictNormal);
+            }
+            if constexpr (!B_MN) {
+              tma_load_2d_pair(b_dst, &tmB, fb, kb * kBK, nb0, kEvictNormal);
+            } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(b_dst + j * 8192, &tmB, &full[s], n0 + j * 64, kb * kBK, kEvictNormal);
+              for (int j = 0; j < BN / CG / 64; ++j)
+                tma_load_2d_pair(b_dst + j * 8192, &tmB, fb, nb0 + j * 64, kb * kBK, kEvictNormal);
+            }
+          } else {
+            mbar_expect_tx(&full[s], Cfg::kStage);
+            if constexpr (!A_MN) {
+              tma_load_2d(a_dst, &tmA, &full[s], kb * kBK, m0, kEvictNormal);
+            } else {
+#pragma unroll
+              for (int j = 0; j < kBM / 64; ++j)
+                tma_load_2d(a_dst + j * 8192, &tmA, &full[s], m0 + j * 64, kb * kBK, kEvictNormal);
+            }
+            if constexpr (!B_MN) {
+              tma_load_2d(b_dst, &tmB, &full[s], kb * kBK, n0, kEvictNormal);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                tma_load_2d(b_dst + j * 8192, &tmB, &full[s], n0 + j * 64, kb * kBK, kEvictNormal);
+            }
           }
           if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
         }
@@ -253,12 +286,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(kBM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    if (lane == 0 && crank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(kBM * CG, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       int s = 0;
       uint32_t ph = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = unit; tile < num_tiles; tile += nunits, ++it) {
         const int as = it & 1;
         const uint32_t aph = (it >> 1) & 1;
         mbar_wait(&tmem_empty[as], aph ^ 1);
@@ -276,12 +309,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                                         : make_smem_desc_sw128(a_addr + kk * 32, 16, 1024);
             const uint64_t bdesc = B_MN ? make_smem_desc_sw128(b_addr + kk * 2048, 8192, 1024)
                                         : make_smem_desc_sw128(b_addr + kk * 32, 16, 1024);
-            umma_ss(d_tmem, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+            if constexpr (CG == 2) umma_ss_pair(d_tmem, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+            else                   umma_ss(d_tmem, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty[s]);  // frees the smem slot once these MMAs have read it
+          // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
+          if constexpr (CG == 2) umma_commit_pair(&empty[s], 0x3); else umma_commit(&empty[s]);
           if (++s == Cfg::kStages) { s = 0; ph ^= 1; }
         }
-        umma_commit(&tmem_full[as]);  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue warps (of both CTAs of a pair)
+        if constexpr (CG == 2) umma_commit_pair(&tmem_full[as], 0x3); else umma_commit(&tmem_full[as]);
         if (dbg != nullptr && it == 0) dbg[4] = clock64();  // all MMAs of the first tile issued
       }
     }
@@ -334,8 +370,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // instead of 16 bytes of 32 different rows.
     const bool can_stage = !p.out_fp32 && !p.accumulate;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int m0 = (tile % num_m) * kBM;
+    for (int tile = unit; tile < num_tiles; tile += nunits, ++it) {
+      const int m0 = (tile % num_m) * (kBM * CG) + static_cast<int>(crank) * kBM;
       const int n0 = (tile / num_m) * BN;
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
@@ -430,16 +466,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+      if (lane == 0) {
+        if (CG == 2 && crank != 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tmem_empty[as]), 0));
+        else mbar_arrive(&tmem_empty[as]);
+      }
       if (dbg != nullptr && it == 0 && threadIdx.x == 64) dbg[6] = clock64();  // first tile stored
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  // A pair leaves together: the leader's commits still arrive on the peer's barriers, and the
+  // peer's epilogue still arrives on the leader's, until both have drained their last tile.
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   if (dbg != nullptr && threadIdx.x == 0) dbg[7] = clock64();
   tc_fence_after();
-  if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  if (warp == 1) {
+    if constexpr (CG == 2) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+    else tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
 }
 
 // ---------------------------------------------------------------------------- host side
@@ -510,11 +554,11 @@ int sm_count() {
   return cached[dev];
 }
 
-template <int BN, bool A_MN, bool B_MN, bool FETCH = false, int EPI = 8>
+template <int BN, bool A_MN, bool B_MN, bool FETCH = false, int CG = 1>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
                        int max_ctas, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN, EPI>;
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, FETCH, EPI>;
+  using Cfg = GemmCfg<BN, CG>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, FETCH, CG>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -523,12 +567,12 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
                                          Cfg::kSmemBytes));
     attr_set[dev & 63] = true;
   }
-  const int num_tiles = ((p.M + kBM - 1) / kBM) * ((p.N + BN - 1) / BN);
-  int grid = sm_count();
-  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
-  if (num_tiles < grid && !FETCH) grid = num_tiles;  // fetch mode keeps every SM pulling chunks
-  DTDS_HOST_CHECK(launch_pdl(kern, dim3(grid), dim3(Cfg::kThreads + (FETCH ? kFetchThreads : 0)),
-                             Cfg::kSmemBytes, stream, tmA, tmB, p));
+  const int num_tiles = ((p.M + kBM * CG - 1) / (kBM * CG)) * ((p.N + BN - 1) / BN);
+  int units = sm_count() / CG;
+  if (max_ctas > 0 && max_ctas / CG < units) units = max_ctas / CG > 0 ? max_ctas / CG : 1;
+  if (num_tiles < units && !FETCH) units = num_tiles;  // fetch mode keeps every SM pulling chunks
+  DTDS_HOST_CHECK(launch_pdl_cluster(kern, dim3(units * CG), dim3(Cfg::kThreads + (FETCH ? kFetchThreads : 0)),
+                                     Cfg::kSmemBytes, stream, static_cast<unsigned>(CG), tmA, tmB, p));
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }
@@ -539,6 +583,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
 // the wrong criterion: a 128-wide tile moves 2/3 of the bytes of two 64-wide ones.
 static int pick_block_n(int M, int N, int K, int requested) {
   if (requested == 64 || requested == 128 || requested == 256) return requested;
+  if (requested == DTDS_GEMM_PAIR + 128 || requested == DTDS_GEMM_PAIR + 256) return requested;
   const int sms = sm_count();
   const int num_m = (M + kBM - 1) / kBM;
   const int num_kb = (K + kBK - 1) / kBK;
@@ -568,17 +613,6 @@ static int pick_block_n(int M, int N, int K, int requested) {
 using namespace dtds;
 
 static long long* g_gemm_dbg = nullptr;
-// 16-warp epilogue variant (not yet run on hardware: opt-in through DTDS_GEMM_WIDE=1 or
-// dtds_gemm_set_wide_epilogue; BLOCK_N 128 / 256, not in all-gather mode).
-static int g_gemm_wide = [] {
-  const char* e = getenv("DTDS_GEMM_WIDE");
-  return e != nullptr && atoi(e) != 0 ? 1 : 0;
-}();
-extern "C" int dtds_gemm_set_wide_epilogue(int on) {
-  const int old = g_gemm_wide;
-  g_gemm_wide = on ? 1 : 0;
-  return old;
-}
 // Development aid: when set, every GEMM CTA writes 8 clock64() stamps (start, setup done, loads
 // issued, first operands landed, MMAs issued, accumulator ready, first tile stored, end) to
 // buf[blockIdx.x * 8 ...].  Pass NULL to switch it off.
@@ -617,7 +651,13 @@ static int gemm_impl(const void* A, const void* B, void* D, const void* bias, co
   if (!a_mn_major) rc = make_tmap_2d_bf16(&tmA, A, K, M, lda, kBK, kBM);
   else             rc = make_tmap_2d_bf16(&tmA, A, M, K, lda, 64, kBK);
   if (rc) return rc;
-  if (!b_mn_major) rc = make_tmap_2d_bf16(&tmB, B, K, N, ldb, kBK, bn);
+  const bool pair = bn >= DTDS_GEMM_PAIR;
+  const int bn_tile = pair ? bn - DTDS_GEMM_PAIR : bn;
+  if (pair && fetch != nullptr) {
+    fprintf(stderr, "[dtds] gemm(all-gather): CTA-pair tiles are not available in this mode\n");
+    return -8;
+  }
+  if (!b_mn_major) rc = make_tmap_2d_bf16(&tmB, B, K, N, ldb, kBK, pair ? bn_tile / 2 : bn_tile);
   else             rc = make_tmap_2d_bf16(&tmB, B, N, K, ldb, 64, kBK);
   if (rc) return rc;
 
@@ -652,17 +692,18 @@ static int gemm_impl(const void* A, const void* B, void* D, const void* bias, co
   }
   const bool f = fetch != nullptr;
 
-  if (g_gemm_wide && !f && bn >= 128) {
-#define DTDS_DISPATCH_WIDE(BN_)                                                                              \
-  if (bn == BN_) {                                                                                           \
-    if (!a_mn_major && !b_mn_major) return launch_gemm<BN_, false, false, false, 16>(tmA, tmB, p, max_ctas, stream); \
-    if (!a_mn_major && b_mn_major) return launch_gemm<BN_, false, true, false, 16>(tmA, tmB, p, max_ctas, stream);   \
-    if (a_mn_major && !b_mn_major) return launch_gemm<BN_, true, false, false, 16>(tmA, tmB, p, max_ctas, stream);   \
-    return launch_gemm<BN_, true, true, false, 16>(tmA, tmB, p, max_ctas, stream);                           \
+  if (pair) {
+#define DTDS_DISPATCH_PAIR(BN_)                                                                                 \
+  if (bn_tile == BN_) {                                                                                         \
+    if (!a_mn_major && !b_mn_major) return launch_gemm<BN_, false, false, false, 2>(tmA, tmB, p, max_ctas, stream); \
+    if (!a_mn_major && b_mn_major) return launch_gemm<BN_, false, true, false, 2>(tmA, tmB, p, max_ctas, stream);   \
+    if (a_mn_major && !b_mn_major) return launch_gemm<BN_, true, false, false, 2>(tmA, tmB, p, max_ctas, stream);   \
+    return launch_gemm<BN_, true, true, false, 2>(tmA, tmB, p, max_ctas, stream);                               \
   }
-    DTDS_DISPATCH_WIDE(128)
-    DTDS_DISPATCH_WIDE(256)
-#undef DTDS_DISPATCH_WIDE
+    DTDS_DISPATCH_PAIR(128)
+    DTDS_DISPATCH_PAIR(256)
+#undef DTDS_DISPATCH_PAIR
+    return -4;
   }
 
 #define DTDS_DISPATCH(BN_)                                                                          \

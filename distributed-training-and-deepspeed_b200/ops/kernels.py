@@ -47,13 +47,11 @@ def _c(t: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------------------- GEMM
 def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, residual=None,
          pre_out=None, dact_in=None, alpha=1.0, out=None, out_dtype=None, accumulate=False,
-         block_n=0, max_ctas=0, ready_flags=None, ready_epoch=0, rows_per_flag=0, split_k=0):
+         block_n=0, max_ctas=0, ready_flags=None, ready_epoch=0, rows_per_flag=0):
     """D[M,N] = act(alpha * A·Bᵀ + bias) (+ residual).
 
     a: [M,K] (or [K,M] when a_mn_major); b: [N,K] (or [K,N] when b_mn_major).  2-D tensors whose
     last dimension is contiguous; row strides must be multiples of 8 elements.
-    split_k >= 2 runs the split-K kernel (block_n 128 or 256, tiles * split_k <= SM count);
-    split_k = 0 lets the autotuner consider it when ``DTDS_SPLITK=1`` (off by default).
     """
     if a_mn_major:
         K, M = a.shape
@@ -84,20 +82,9 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
     assert out.stride(-1) == 1 and out.shape == (M, N)
     out_fp32 = out.dtype == torch.float32
     L = _lib.lib()
-    if split_k >= 2 and block_n not in (128, 256):
-        block_n = 128   # the split-K kernel has 128- and 256-wide tiles only
     if block_n == 0 and ready_flags is None:
         block_n = _tuned_block_n(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn_major,
                                  b_mn_major, act, out_fp32, alpha)
-        if split_k == 0 and _SPLITK and max_ctas == 0:
-            block_n, split_k = _tuned_splitk(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn_major,
-                                             b_mn_major, act, out_fp32, alpha, block_n)
-    if split_k >= 2:
-        assert ready_flags is None and max_ctas == 0, "split-K excludes the all-gather mode and CTA caps"
-        rc = _splitk_call(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn_major, b_mn_major,
-                          act, out_fp32, accumulate, alpha, block_n, split_k)
-        _lib.check(rc, "dtds_gemm_bf16_splitk")
-        return out
     rc = L.dtds_gemm_bf16_ex(
         a.data_ptr(), b.data_ptr(), out.data_ptr(), _lib.ptr(bias), _lib.ptr(residual),
         _lib.ptr(pre_out), _lib.ptr(dact_in), M, N, K, a.stride(0), b.stride(0), out.stride(0),
@@ -108,107 +95,6 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
         _lib.stream_ptr())
     _lib.check(rc, "dtds_gemm_bf16_ex")
     return out
-
-
-def set_wide_epilogue(on: bool) -> bool:
-    """16-warp GEMM epilogue on/off (see dtds_gemm_set_wide_epilogue); returns the previous setting.
-    The BLOCK_N autotune cache is cleared because the ranking may change."""
-    _tune_cache.clear()
-    return bool(_lib.lib().dtds_gemm_set_wide_epilogue(int(bool(on))))
-
-
-# ---- split-K (csrc/gemm_splitk_sm100.cu): off unless DTDS_SPLITK=1 or split_k is passed ----------
-_SPLITK = os.environ.get("DTDS_SPLITK", "0") != "0"
-_splitk_bufs: dict = {}
-_splitk_cache: dict = {}
-
-
-def _splitk_buffers(L, device, M, N, block_n, splits):
-    """(workspace, counters) of the current stream; launches on different streams may overlap on
-    the GPU and must not share partial-sum storage."""
-    need = L.dtds_gemm_splitk_workspace_bytes(M, N, block_n, splits)
-    tiles = L.dtds_gemm_splitk_tiles(M, N, block_n)
-    key = (device, _lib.stream_ptr())
-    ws, flags = _splitk_bufs.get(key, (None, None))
-    if ws is None or ws.numel() * 4 < need or flags.numel() < tiles:
-        ws = torch.empty(max(need // 4, 1 << 20), dtype=torch.float32, device=device)
-        flags = torch.zeros(max(tiles, 256), dtype=torch.int32, device=device)
-        _splitk_bufs[key] = (ws, flags)
-    return ws, flags
-
-
-def _splitk_call(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn, b_mn, act, out_fp32,
-                 accumulate, alpha, block_n, splits):
-    ws, flags = _splitk_buffers(L, a.device, M, N, block_n, splits)
-    return L.dtds_gemm_bf16_splitk(
-        a.data_ptr(), b.data_ptr(), out.data_ptr(), _lib.ptr(bias), _lib.ptr(residual), _lib.ptr(pre_out),
-        _lib.ptr(dact_in), M, N, K, a.stride(0), b.stride(0), out.stride(0),
-        residual.stride(0) if residual is not None else 0, dact_in.stride(0) if dact_in is not None else 0,
-        int(a_mn), int(b_mn), int(act), int(out_fp32), int(accumulate), float(alpha), int(block_n), int(splits),
-        ws.data_ptr(), flags.data_ptr(), _lib.stream_ptr())
-
-
-def splitk_candidates(L, device, M, N, K):
-    """(block_n, splits) pairs that keep every (tile, split) unit resident and leave each split at
-    least four 64-wide k-blocks."""
-    sms = torch.cuda.get_device_properties(device).multi_processor_count
-    num_kb = (K + 63) // 64
-    out = []
-    for bn in (128, 256):
-        if bn == 256 and N <= 128:
-            continue
-        tiles = L.dtds_gemm_splitk_tiles(M, N, bn)
-        for s in (2, 3, 4, 6, 8):
-            if tiles * s <= sms and num_kb // s >= 4:
-                out.append((bn, s))
-    return out
-
-
-def _tuned_splitk(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn, b_mn, act, out_fp32, alpha, bn_plain):
-    """Times the plain kernel at its tuned BLOCK_N against the split-K candidates (first eager call
-    of a shape only; never during capture) and returns (block_n, splits)."""
-    key = (M, N, K, a_mn, b_mn, int(act), bias is not None, residual is not None, pre_out is not None,
-           dact_in is not None, out_fp32, a.stride(0), b.stride(0), out.stride(0))
-    hit = _splitk_cache.get(key)
-    if hit is not None:
-        return hit
-    if torch.cuda.is_current_stream_capturing():
-        return bn_plain, 1
-    cands = splitk_candidates(L, a.device, M, N, K)
-    if not cands:
-        _splitk_cache[key] = (bn_plain, 1)
-        return bn_plain, 1
-    tmp = torch.empty_strided(out.shape, out.stride(), dtype=out.dtype, device=out.device)
-    tmp_pre = torch.empty_strided(pre_out.shape, pre_out.stride(), dtype=pre_out.dtype, device=out.device) \
-        if pre_out is not None else None
-    stream = _lib.stream_ptr()
-
-    def plain():
-        return L.dtds_gemm_bf16_ex(
-            a.data_ptr(), b.data_ptr(), tmp.data_ptr(), _lib.ptr(bias), _lib.ptr(residual), _lib.ptr(tmp_pre),
-            _lib.ptr(dact_in), M, N, K, a.stride(0), b.stride(0), tmp.stride(0),
-            residual.stride(0) if residual is not None else 0, dact_in.stride(0) if dact_in is not None else 0,
-            int(a_mn), int(b_mn), int(act), int(out_fp32), 0, float(alpha), bn_plain, 0, None, 0, 0, stream)
-
-    def timed(fn):
-        if fn() != 0:
-            return float("inf")
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(4):
-            fn()
-        e1.record()
-        e1.synchronize()
-        return e0.elapsed_time(e1)
-
-    best, best_t = (bn_plain, 1), timed(plain)
-    for bn, s in cands:
-        t = timed(lambda: _splitk_call(L, a, b, tmp, bias, residual, tmp_pre, dact_in, M, N, K, a_mn, b_mn, act,
-                                       out_fp32, False, alpha, bn, s))
-        if t < 0.97 * best_t:   # ask for a real margin before leaving the profiled kernel
-            best, best_t = (bn, s), t
-    _splitk_cache[key] = best
-    return best
 
 
 _tune_cache: dict = {}

@@ -23,26 +23,9 @@ extern "C" {
 #define DTDS_ACT_GELU_ERF 2  /* HF BERT hidden_act="gelu" (model/bert_mp.py:22-24) */
 #define DTDS_ACT_GELU_TANH 3 /* BLOOM (zero_dp_training.py:117) */
 
-/* Split-K variant of dtds_gemm_bf16_ex (csrc/gemm_splitk_sm100.cu) for GEMMs whose tile count
- * leaves most SMs idle (N = hidden projections and their dgrads at a few thousand tokens: 48-96
- * tiles, K up to 4*hidden).  `splits` CTAs share each output tile, each over 1/splits of K; the
- * partial tiles meet in `workspace` (fp32, dtds_gemm_splitk_workspace_bytes) and the split-0 CTA
- * applies the same fused epilogue.  block_n is 128 or 256; tiles * splits must not exceed the SM
- * count and splits must not exceed K/64; `flags` holds one zeroed uint32 per tile
- * (dtds_gemm_splitk_tiles) and is left zeroed.  Launches that may overlap on the GPU need
- * separate workspaces.  The reference has no counterpart (cuBLAS picks its own split-K). */
-/* Switches dtds_gemm_bf16 / _ex between the 8-warp epilogue (default) and a 16-warp one (four
- * warps per TMEM lane quadrant; BLOCK_N 128 / 256, not the all-gather mode).  Returns the previous
- * setting.  Also set by DTDS_GEMM_WIDE=1 at load time. */
-int dtds_gemm_set_wide_epilogue(int on);
-int dtds_gemm_splitk_tiles(int M, int N, int block_n);
-size_t dtds_gemm_splitk_workspace_bytes(int M, int N, int block_n, int splits);
-int dtds_gemm_bf16_splitk(const void* A, const void* B, void* D, const void* bias,
-                          const void* residual, void* pre_out, const void* dact_in, int M, int N,
-                          int K, int lda, int ldb, int ldd, int ld_res, int ld_dact, int a_mn_major,
-                          int b_mn_major, int act, int out_fp32, int accumulate, float alpha,
-                          int block_n, int splits, float* workspace, unsigned* flags,
-                          cudaStream_t stream);
+/* Added to `block_n` (128 or 256) of dtds_gemm_bf16_ex: 256 x block_n tiles computed by a pair of
+ * CTAs on neighbouring SMs (tcgen05 cta_group::2), each staging half of the B tile. */
+#define DTDS_GEMM_PAIR 1024
 
 /* ---- tcgen05 / TMEM / TMA GEMM (replaces cuBLAS behind nn.Linear: model/transformer.py:37-40,
  *      50-51; BertLayer / BertOnlyMLMHead in model/bert_mp.py:22-24) -------------------------
