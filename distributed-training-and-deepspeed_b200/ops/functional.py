@@ -14,7 +14,6 @@ pack or unpack copies ("DDP variant writes dW straight into th
 from __future__ import annotations
 
 import os
-import itertools
 import math
 
 import torch
@@ -22,7 +21,8 @@ import torch
 from . import kernels as K
 from .reference import ACT_NONE
 
-_seed_counter = itertools.count(0x5EED)
+_SEED_START = 0x5EED
+_seed_counter = _SEED_START
 _base_seed = 0
 
 
@@ -30,11 +30,26 @@ def manual_seed(seed: int) -> None:
     """Seeds the dropout streams of the fused kernels (independent of torch's generator)."""
     global _seed_counter, _base_seed
     _base_seed = int(seed) & 0xFFFFFFFF
-    _seed_counter = itertools.count(0x5EED)
+    _seed_counter = _SEED_START
 
 
 def next_seed() -> int:
-    return ((_base_seed << 32) ^ (next(_seed_counter) * 0x9E3779B1)) & 0x7FFFFFFFFFFFFFFF
+    global _seed_counter
+    n = _seed_counter
+    _seed_counter = n + 1
+    return ((_base_seed << 32) ^ (n * 0x9E3779B1)) & 0x7FFFFFFFFFFFFFFF
+
+
+def get_seed_state() -> tuple:
+    """Position of the host-side dropout seed stream.  Code that re-runs a forward and needs the
+    SAME masks (activation recomputation) saves it before the first run and restores it with
+    `set_seed_state` before the re-run."""
+    return (_base_seed, _seed_counter)
+
+
+def set_seed_state(state: tuple) -> None:
+    global _seed_counter, _base_seed
+    _base_seed, _seed_counter = state
 
 
 # ------------------------------------------------------------------ gradient emission helpers

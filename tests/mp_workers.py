@@ -328,6 +328,45 @@ def pipeline_matches_single_process(rank, world, chunks=4):
     assert set(idle.keys()) == set(range(world))
 
 
+def pipeline_recompute_replays_dropout(rank, world, chunks=4):
+    """GPipe with dropout > 0: gradients with activation recomputation ('except_last') equal the
+    gradients without it ('never') when both runs start from the same dropout seed state -- the
+    recomputed forward must regenerate the masks of the first forward."""
+    from dtds_b200.models import get_config
+    from dtds_b200.models.bert_mp import BertModelWithMP
+    from dtds_b200.ops import functional as Fn
+    dev = _dev(rank)
+    dtype = torch.bfloat16 if dev.type == "cuda" else torch.float32
+    cfg = get_config("bert-tiny").replace(hidden_dropout_prob=0.2, attention_probs_dropout_prob=0.2,
+                                          num_hidden_layers=4)
+    torch.manual_seed(0)
+    bert = BertModelWithMP(cfg, dtype=dtype)
+    bert.train()
+    B, S = 8, 128
+    g = torch.Generator().manual_seed(3)
+    ids = torch.randint(0, cfg.vocab_size, (B, S), generator=g)
+    labels = ids.clone()
+    labels[:, ::3] = -100
+    pipe = bert.to_pipeline(chunks)
+    grads = {}
+    for mode in ("never", "except_last"):
+        for p in bert.parameters():
+            p.grad = None
+            if getattr(p, "main_grad", None) is not None:
+                p.main_grad.zero_()
+        Fn.manual_seed(77)
+        bert._stage().checkpoint = mode
+        pipe.forward_backward(ids, labels)
+        grads[mode] = [(n, (p.grad if p.grad is not None else p.main_grad).float().clone())
+                       for n, p in bert.named_parameters() if p.requires_grad and
+                       (p.grad is not None or getattr(p, "main_grad", None) is not None)]
+    assert grads["never"], "no gradients recorded"
+    for (n, a), (_, b) in zip(grads["never"], grads["except_last"]):
+        denom = a.abs().max().item() + 1e-6
+        err = (a - b).abs().max().item() / denom
+        assert err < (2e-2 if dtype == torch.bfloat16 else 1e-5), f"{n}: recompute changed the gradient by {err}"
+
+
 def allgather_gemm_matches_gathered(rank, world):
     """The all-gather fused GEMM (weights pulled from peer shards by the kernel's fetch warps)
     equals the GEMM on a weight that was gathered beforehand; forward and dgrad forms."""

@@ -34,6 +34,10 @@ def test_gpipe_matches_single_process_gloo():
     run_distributed("pipeline_matches_single_process", world=2, backend="gloo", args=(4,), timeout=600)
 
 
+def test_gpipe_recompute_replays_dropout_gloo():
+    run_distributed("pipeline_recompute_replays_dropout", world=2, backend="gloo", args=(4,), timeout=600)
+
+
 def test_zero_checkpoint_resume_gloo():
     run_distributed("zero_checkpoint_resume", world=2, backend="gloo", args=(2,), timeout=600)
     run_distributed("zero_checkpoint_resume", world=2, backend="gloo", args=(3,), timeout=600)

@@ -64,6 +64,10 @@ def test_pipeline_matches_single_process(chunks):
     run_distributed("pipeline_matches_single_process", world=2, backend="nccl", args=(chunks,), timeout=600)
 
 
+def test_pipeline_recompute_replays_dropout():
+    run_distributed("pipeline_recompute_replays_dropout", world=2, backend="nccl", args=(4,), timeout=600)
+
+
 def test_allgather_fused_gemm():
     run_distributed("allgather_gemm_matches_gathered", world=2, backend="nccl")
 
