@@ -65,6 +65,7 @@ class FusedAdam(torch.optim.Optimizer):
             self._groups.append(_FlatGroup(f))
         # ---- optional: update each bucket as soon as its gradients are final, under backward
         self.overlap = bool(overlap_with_backward)
+        self._stepped = False      # host-side: has any update run yet (see _rebind)
         self._done: dict = {}      # id(group) -> list of (lo, hi) ranges already updated this step
         self._obuckets = []        # (group, lo, hi, params)
         self._opt_streams: dict = {}
@@ -125,7 +126,11 @@ class FusedAdam(torch.optim.Optimizer):
                 o_old, o_new, n = old.offsets[_index_of(old.params, p)], p._flat_offset, p._numel
                 ng.exp_avg[o_new:o_new + n].copy_(grp.exp_avg[o_old:o_old + n])
                 ng.exp_avg_sq[o_new:o_new + n].copy_(grp.exp_avg_sq[o_old:o_old + n])
-                if ng.lowp and grp.lowp:
+                # Masters captured at construction are only worth carrying once this optimizer has
+                # updated them.  Before the first step the engine's buffer is the truth: DDP has
+                # broadcast rank 0's weights into it since (the old masters still hold this rank's
+                # pre-broadcast values) and _FlatGroup(new) has just derived masters from it.
+                if ng.lowp and grp.lowp and self._stepped:
                     ng.master[o_new:o_new + n].copy_(grp.master[o_old:o_old + n])
             ng.step.copy_(grp.step)
             new_groups.append(ng)
@@ -192,6 +197,7 @@ class FusedAdam(torch.optim.Optimizer):
             with torch.cuda.stream(side):
                 run()
         self._done.setdefault(id(group), []).append((lo, hi))
+        self._stepped = True
 
     @property
     def flats(self):
@@ -264,13 +270,25 @@ class FusedAdam(torch.optim.Optimizer):
         self._rebind()
         for g, s in zip(self.param_groups, sd["param_groups"]):
             g.update(s)
-        for grp, s in zip(self._groups, sd["flat_state"]):
+        flat_state = sd["flat_state"]
+        if len(flat_state) != len(self._groups):
+            raise ValueError(f"FusedAdam.load_state_dict: checkpoint has {len(flat_state)} flat groups, this "
+                             f"optimizer has {len(self._groups)} (different wrap order or device placement?)")
+        for i, (grp, s) in enumerate(zip(self._groups, flat_state)):
+            want = (grp.lo, grp.hi, grp.exp_avg.numel())
+            got = (s.get("lo", grp.lo), s.get("hi", grp.hi), s["exp_avg"].numel())
+            if want != got:
+                raise ValueError(f"FusedAdam.load_state_dict: flat group {i} covers elements [{want[0]}, {want[1]}) "
+                                 f"({want[2]} values) here but [{got[0]}, {got[1]}) ({got[2]} values) in the checkpoint; "
+                                 "it was written with another parameter layout or world size")
+        for grp, s in zip(self._groups, flat_state):
             grp.master.copy_(s["master"])
             grp.exp_avg.copy_(s["exp_avg"])
             grp.exp_avg_sq.copy_(s["exp_avg_sq"])
             grp.step.copy_(s["step"])
             if grp.lowp:
                 grp.flat.param_flat[grp.lo:grp.hi].copy_(grp.master)
+        self._stepped = True   # the masters now carry trained values (see _rebind)
 
 
 def _index_of(params, p) -> int:

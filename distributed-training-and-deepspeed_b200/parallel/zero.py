@@ -29,6 +29,8 @@ On CPU/gloo, or with ``DTDS_COMM=nccl``, the same schedule runs on library colle
 """
 from __future__ import annotations
 
+import math
+
 import os
 
 import torch
@@ -45,6 +47,8 @@ class _ZBucket:
 
     def __init__(self, index, lo, hi, world, params):
         self.index, self.lo, self.hi = index, lo, hi
+        assert (hi - lo) % (8 * world) == 0, \
+            f"bucket [{lo}, {hi}) is not divisible into {world} slices of whole 16-byte vectors"
         self.per = (hi - lo) // world
         self.params, self.pending, self.launched = params, 0, False
         self.state_off = 0
@@ -152,7 +156,10 @@ class ZeroEngine(nn.Module):
         wd = float(op.get("weight_decay", 0.0))
         # DeepSpeed maps "Adam" to FusedAdam with adam_w_mode=True; "AdamW" likewise.
         self.adamw_mode = bool(op.get("adam_w_mode", True))
-        align = max(64, 8 * self.world)
+        # every parameter offset (hence every bucket edge) and the total are multiples of
+        # lcm(64, 8*world): buckets split evenly over the ranks in whole 16-byte vectors for any
+        # world size (3, 5, 6, 7 included), none of the tail is left unreduced
+        align = math.lcm(64, 8 * self.world)
         self.flat = FlatBuffers(params, symmetric=True, group=process_group, align=align,
                                 pad_total_to=align)
         self.lowp = self.flat.param_dtype != torch.float32

@@ -92,25 +92,25 @@ def load_checkpoint(path: str, model, optimizer=None, strict: bool = True) -> in
     target = _unwrap(model)
     if _stage_partitioned(model):
         target = getattr(target, "bert", target)   # each stage loads the keys of its own modules
-        with torch.no_grad():
-            for k, v in target.state_dict().items():
-                if k not in sd:
-                    raise KeyError(f"checkpoint lacks {k}")
-                v.copy_(sd[k].to(v.dtype))
-    if optimizer is not None and os.path.exists(os.path.join(path, f"optim_rank{rank}.pt")):
-        osd = torch.load(os.path.join(path, f"optim_rank{rank}.pt"), map_location="cpu", weights_only=False)
-        optimizer.load_state_dict(osd)   # restores fp32 masters and re-derives the working parameters
-    else:
-        if getattr(model, "param3", None) is not None:
-            raise RuntimeError("loading a ZeRO-3 engine needs its optimizer shards (sharded parameters)")
+    sharded_params = getattr(model, "param3", None) is not None
+    have_optim = optimizer is not None and os.path.exists(os.path.join(path, f"optim_rank{rank}.pt"))
+    if sharded_params and not have_optim:
+        raise RuntimeError("loading a ZeRO-3 engine needs its optimizer shards (sharded parameters)")
+    # 1. model.pt -> module, always: parameters an optimizer does not own (frozen ones, plain
+    #    torch.optim optimizers that keep no master copy) and buffers come from nowhere else.
+    if not sharded_params:
         with torch.no_grad():
             own = target.state_dict()
             missing = [k for k in own if k not in sd]
-            if strict and missing:
+            if (strict or _stage_partitioned(model)) and missing:
                 raise KeyError(f"checkpoint lacks {missing[:5]}")
             for k, v in own.items():
                 if k in sd:
                     v.copy_(sd[k].to(v.dtype))
+    # 2. optimizer shard: engine optimizers then overwrite what they own with their fp32 masters
+    if have_optim:
+        osd = torch.load(os.path.join(path, f"optim_rank{rank}.pt"), map_location="cpu", weights_only=False)
+        optimizer.load_state_dict(osd)
     if world > 1:
         dist.barrier()
     return int(meta["step"])

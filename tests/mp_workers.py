@@ -170,6 +170,47 @@ def ddp_matches_single_process(rank, world, bucket_mb=0.05, sparse=False):
     assert err2 < (0.08 if dtype == torch.bfloat16 else 1e-4), err2
 
 
+def optimizer_built_before_ddp_wrap(rank, world):
+    """The reference builds the optimizer before wrapping the model (data_parallel_training.py:34-44).
+    With low-precision parameters the optimizer captured fp32 masters of THIS rank's initial weights;
+    the wrap then broadcasts rank 0's.  After the first step all replicas must still be identical and
+    equal to a run where the optimizer was built after the wrap."""
+    from dtds_b200.optim import FusedAdam
+    from dtds_b200.parallel.ddp import DistributedDataParallel
+    dev = _dev(rank)
+    dtype = torch.bfloat16
+
+    def run(opt_first):
+        cfg, model = _tiny_bert(dev, dtype, seed=100 + rank)   # replicas start DIFFERENT
+        if opt_first:
+            opt = FusedAdam(model.parameters(), lr=1e-2)
+            ddp = DistributedDataParallel(model, bucket_cap_mb=0.05)
+        else:
+            ddp = DistributedDataParallel(model, bucket_cap_mb=0.05)
+            opt = FusedAdam(model.parameters(), lr=1e-2)
+        g = torch.Generator().manual_seed(9)
+        ids = torch.randint(0, cfg.vocab_size, (2, 128), generator=g).to(dev)
+        labels = ids.clone()
+        labels[:, ::2] = -100
+        for _ in range(2):
+            opt.zero_grad()
+            ddp(ids, labels=labels).loss.backward()
+            opt.step()
+        if dev.type == "cuda":
+            torch.cuda.synchronize()
+        return torch.cat([p.detach().float().flatten() for p in model.parameters()]).cpu()
+
+    a, b = run(True), run(False)
+    assert torch.equal(a, b), f"optimizer-first differs from wrap-first by {(a - b).abs().max().item()}"
+    parts = [torch.empty_like(a) for _ in range(world)] if dev.type != "cuda" else None
+    import torch.distributed as dist
+    mine = a.to(dev) if dev.type == "cuda" else a
+    gathered = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(gathered, mine)
+    for r in range(world):
+        assert torch.equal(gathered[r].cpu(), a), f"replica {r} diverged from replica {rank}"
+
+
 def ddp_training_loop(rank, world, use_graph=False, fuse_opt=False, sparse=False):
     """A few optimizer steps under DDP; all ranks must hold identical parameters afterwards.
     fuse_opt: Adam runs per bucket on the communication stream right behind the bucket's

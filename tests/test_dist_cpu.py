@@ -26,6 +26,15 @@ def test_ddp_fused_optimizer_gloo(sparse):
     run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False, True, sparse))
 
 
+def test_optimizer_built_before_ddp_wrap_gloo():
+    run_distributed("optimizer_built_before_ddp_wrap", world=2, backend="gloo")
+
+
+def test_zero_stages_world3_gloo():
+    """Bucket edges must split evenly over 3 ranks (8*world does not divide 64)."""
+    run_distributed("zero_stages_match_stage0", world=3, backend="gloo", timeout=900)
+
+
 def test_zero_stages_match_stage0_gloo():
     run_distributed("zero_stages_match_stage0", world=2, backend="gloo", timeout=600)
 

@@ -68,6 +68,10 @@ def test_pipeline_recompute_replays_dropout():
     run_distributed("pipeline_recompute_replays_dropout", world=2, backend="nccl", args=(4,), timeout=600)
 
 
+def test_optimizer_built_before_ddp_wrap():
+    run_distributed("optimizer_built_before_ddp_wrap", world=2, backend="nccl")
+
+
 def test_allgather_fused_gemm():
     run_distributed("allgather_gemm_matches_gathered", world=2, backend="nccl")
 
