@@ -200,6 +200,21 @@ def main():
     e2e_wall_ms = (time.perf_counter() - t0) * 1e3
     e2e_ms = max(f0.elapsed_time(f1), e2e_wall_ms)
 
+    evidence = describe.pop("_evidence", {})
+    flat = describe.pop("_flat", None)
+    if world > 1 and flat is not None:
+        # every replica must hold bit-identical parameters after K + W + K steps
+        bits = flat.param_flat.view(torch.int16).to(torch.int64)
+        idx = torch.arange(bits.numel(), device=dev, dtype=torch.int64) % 8191 + 1
+        cs = torch.stack([bits.sum(), (bits * idx).sum()])
+        allcs = [torch.empty_like(cs) for _ in range(world)]
+        dist.all_gather(allcs, cs)
+        evidence["replicas_identical"] = bool(all(torch.equal(c, allcs[0]) for c in allcs))
+        evidence["param_checksum"] = [int(x) for x in allcs[0].tolist()]
+        assert evidence["replicas_identical"], f"replicas diverged: {[c.tolist() for c in allcs]}"
+        if "grad_vs_nccl_max_rel" in evidence:
+            assert evidence["grad_vs_nccl_max_rel"] < 3e-2, evidence
+
     t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -222,6 +237,7 @@ def main():
                 "h2d_bytes_per_step": 2 * B * S * 8, "d2h_bytes_per_step": 4},
         "gpu_launches": launches_per_step * args.steps,
         "final_loss": final_loss,
+        **evidence,
     }
     if rank == 0:
         print(json.dumps(out))
@@ -247,8 +263,6 @@ def build_ours(args, cfg, dev, world, ids_h, labels_h):
     overlap = not args.no_overlap_optimizer
     opt = HFAdamW(model.parameters(), lr=5e-5, overlap_with_backward=overlap and world == 1,
                   overlap_bucket_mb=args.adam_bucket_mb)
-    if overlap and world > 1:
-        net.fuse_optimizer(opt)
 
     def train_step(ids, labels):
         opt.zero_grad()
@@ -258,13 +272,81 @@ def build_ours(args, cfg, dev, world, ids_h, labels_h):
         return loss
 
     ex = [ids_h[0].to(dev), labels_h[0].to(dev)]
-    n0 = _lib.launch_count()
-    train_step(*ex)
+    evidence = {}
+    if world > 1:
+        evidence.update(_check_bucket_against_nccl(net, ex, world))
+    if overlap and world > 1:
+        net.fuse_optimizer(opt)
+    # count one eager step: launches of this library by C entry point, and library (NCCL) collectives
+    n0, c0 = _lib.launch_count(), dict(_lib.call_counts)
+    with _count_torch_collectives() as nccl_calls:
+        train_step(*ex)
     per_step = _lib.launch_count() - n0
+    calls = {k: v - c0.get(k, 0) for k, v in _lib.call_counts.items() if v - c0.get(k, 0)}
+    evidence["comm_kernel_calls_per_step"] = {k: v for k, v in calls.items()
+                                              if any(t in k for t in ("allreduce", "all_reduce", "reduce_scatter",
+                                                                      "allgather", "all_gather", "zero_step", "broadcast"))}
+    evidence["nccl_collective_calls_per_step"] = dict(nccl_calls)
+    describe = {"native_kernels": True, "_evidence": evidence, "_flat": getattr(net, "flat", None)}
     if args.no_graph:
-        return train_step, train_step, per_step, {"execution": "eager launches", "native_kernels": True}
+        return train_step, train_step, per_step, {"execution": "eager launches", **describe}
     gs = GraphedStep(train_step, ex, warmup=2)
-    return train_step, gs, per_step, {"execution": "whole step replayed as one CUDA graph", "native_kernels": True}
+    return train_step, gs, per_step, {"execution": "whole step replayed as one CUDA graph", **describe}
+
+
+class _count_torch_collectives:
+    """Counts torch.distributed collective calls (i.e. NCCL) made while active."""
+    NAMES = ("all_reduce", "all_gather_into_tensor", "reduce_scatter_tensor", "broadcast", "all_gather", "reduce")
+
+    def __enter__(self):
+        import torch.distributed as dist
+        self.counts, self._saved = {}, {}
+        for n in self.NAMES:
+            fn = getattr(dist, n, None)
+            if fn is None:
+                continue
+            self._saved[n] = fn
+
+            def wrapped(*a, _n=n, _fn=fn, **k):
+                self.counts[_n] = self.counts.get(_n, 0) + 1
+                return _fn(*a, **k)
+            setattr(dist, n, wrapped)
+        return self.counts
+
+    def __exit__(self, *exc):
+        import torch.distributed as dist
+        for n, fn in self._saved.items():
+            setattr(dist, n, fn)
+        return False
+
+
+def _check_bucket_against_nccl(net, ex, world):
+    """One eager forward/backward without communication, NCCL all-reduce of a saved fp32 copy of the
+    local gradients, then the same pass through the engine's own bucket kernels: the averaged
+    gradient buffer must agree within bf16 rounding."""
+    import torch
+    import torch.distributed as dist
+    from dtds_b200.ops import functional as F
+    flat = net.flat
+    F.manual_seed(4242)
+    with net.no_sync():
+        net(ex[0], labels=ex[1]).loss.backward()
+    torch.cuda.synchronize()
+    want = flat.grad_flat.float().clone()
+    dist.all_reduce(want)
+    want /= world
+    F.manual_seed(4242)          # same dropout masks in the second pass
+    net._accumulating = False    # drop the accumulated local gradients: start a fresh iteration
+    net(ex[0], labels=ex[1]).loss.backward()
+    torch.cuda.synchronize()
+    got = flat.grad_flat.float()
+    worst = 0.0
+    for b in net.buckets:
+        w, g = want[b.lo:b.hi], got[b.lo:b.hi]
+        worst = max(worst, ((g - w).abs().max() / (w.abs().max() + 1e-12)).item())
+    for p in flat.params:
+        p.grad = None
+    return {"grad_vs_nccl_max_rel": worst, "grad_vs_nccl_buckets": len(net.buckets)}
 
 
 def build_torch_baseline(args, cfg, dev, world, local):
@@ -290,7 +372,7 @@ def build_torch_baseline(args, cfg, dev, world, local):
         return loss
 
     return train_step, train_step, 0, {"execution": "torch eager (HF BERT + torch DDP/NCCL + AdamW, bf16 autocast)",
-                                       "native_kernels": False}
+                                       "native_kernels": False, "_evidence": {}, "_flat": None}
 
 
 if __name__ == "__main__":
