@@ -9,9 +9,8 @@
 // IPC and maps every peer's copy; kernels receive a device table of the n peer addresses and of
 // the n signal pads.  Through NVSwitch every peer is at full NVLink bandwidth, so there is no
 // ring: each rank pulls its 1/n slice from all peers at once (reduce-scatter phase) and pushes
-// the result to all peers at once (all-gather phase).  Cross-GPU ordering uses flag words in the
-// signal pads with release/acquire at system scope; the flags are consumed by the waiter
-// (CAS 1->0), so the pads are reusable launch after launch without epochs.
+// the result to all peers at once (all-gather phase).  Cross-GPU ordering uses epoch flag words in
+// the signal pads with release/acquire at system scope (one remote store per peer per barrier).
 //
 // Kernels here: barrier, one-shot all-reduce (latency-bound sizes), two-shot all-reduce
 // (bandwidth-bound sizes; scale and dtype conversion fused), reduce-scatter, all-gather,
@@ -41,36 +40,52 @@ struct PeerTable {
 };
 
 // ------------------------------------------------------------------------- signalling
-__device__ __forceinline__ void signal_send(uint32_t* addr) {
-  uint32_t spins = 0, old;
-  do {
-    asm volatile("atom.release.sys.global.cas.b32 %0, [%1], 0, 1;" : "=r"(old) : "l"(addr) : "memory");
-    if (++spins > DTDS_SPIN_LIMIT) {
-      printf("[dtds] comm: signal_send stuck (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-      __trap();
-    }
-  } while (old != 0);
+// Signal pad layout (per rank, zero-initialised once at allocation, never reset):
+//   flags  [kSlots][kMaxCommBlocks][kMaxRanks] u32 : flags[slot][block][src] is written only by rank
+//                                                    `src` (block `block` of its kernel)
+//   epochs [kSlots][kMaxCommBlocks]            u32 : this rank's own arrival count per (slot, block)
+// A barrier is ONE fire-and-forget remote store per peer plus a spin on local memory: the block
+// bumps its private epoch e, stores e into its flag word on every peer (st.release.sys: all earlier
+// writes of the block are visible first) and waits until every peer's word in its own pad has
+// reached e (ld.acquire.sys).  Epochs only grow, so nothing is consumed or reset and no remote
+// atomic round trip is paid (the first version CAS-ed every flag 0->1 remotely and 1->0 locally:
+// two NVLink round trips per barrier).  All ranks issue the same collectives with the same grid
+// sizes in the same order on the streams that share a pad, so block b's epochs advance in lockstep
+// on every rank; comparison is wrap-safe (signed difference).
+constexpr int kSlots = 4;
+constexpr size_t kFlagWords = static_cast<size_t>(kSlots) * kMaxCommBlocks * kMaxRanks;
+constexpr size_t kEpochWords = static_cast<size_t>(kSlots) * kMaxCommBlocks;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* addr, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
 }
-__device__ __forceinline__ void signal_wait(uint32_t* addr) {
-  uint32_t spins = 0, old;
-  do {
-    asm volatile("atom.acquire.sys.global.cas.b32 %0, [%1], 1, 0;" : "=r"(old) : "l"(addr) : "memory");
-    if (++spins > DTDS_SPIN_LIMIT) {
-      printf("[dtds] comm: signal_wait stuck (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-      __trap();
-    }
-  } while (old != 1);
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* addr) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
 }
 // Block-level barrier across all ranks: block b of every rank meets block b of every other rank.
 // `slot` selects an independent flag set (0 = entry barrier, 1 = exit barrier, ...).
 __device__ __forceinline__ void cross_gpu_barrier(const PeerTable& pt, int slot) {
-  __syncthreads();
+  __syncthreads();   // every thread's earlier global writes happen-before the releasing stores below
   if (threadIdx.x < pt.world) {
     const int peer = threadIdx.x;
-    const size_t base = (static_cast<size_t>(slot) * kMaxCommBlocks + blockIdx.x) * kMaxRanks;
-    __threadfence_system();
-    signal_send(pt.signal[peer] + base + pt.rank);
-    signal_wait(pt.signal[pt.rank] + base + peer);
+    const size_t cell = static_cast<size_t>(slot) * kMaxCommBlocks + blockIdx.x;
+    uint32_t* my_epoch = pt.signal[pt.rank] + kFlagWords + cell;
+    const uint32_t e = *reinterpret_cast<volatile uint32_t*>(my_epoch) + 1;
+    __syncwarp((1u << pt.world) - 1u);         // everyone has read the old epoch
+    if (peer == 0) *reinterpret_cast<volatile uint32_t*>(my_epoch) = e;
+    __threadfence_system();                    // cumulativity: the block's writes, then the flag
+    st_release_sys(pt.signal[peer] + cell * kMaxRanks + pt.rank, e);
+    const uint32_t* mine = pt.signal[pt.rank] + cell * kMaxRanks + peer;
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - e) < 0) {
+      if (++spins > DTDS_SPIN_LIMIT) {
+        printf("[dtds] comm: barrier slot %d block %d: rank %d never saw epoch %u from rank %d\n", slot,
+               blockIdx.x, pt.rank, e, peer);
+        __trap();
+      }
+    }
   }
   __syncthreads();
 }
@@ -449,7 +464,7 @@ extern "C" int dtds_symm_close(unsigned long long ptr) {
   return 0;
 }
 extern "C" size_t dtds_signal_pad_bytes() {
-  return static_cast<size_t>(4) * kMaxCommBlocks * kMaxRanks * sizeof(uint32_t);
+  return (kFlagWords + kEpochWords) * sizeof(uint32_t);
 }
 
 // ---- collectives ----------------------------------------------------------------------------

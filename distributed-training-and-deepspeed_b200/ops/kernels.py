@@ -97,12 +97,13 @@ def gemm(a, b, *, a_mn_major=False, b_mn_major=False, bias=None, act=ACT_NONE, r
     return out
 
 
+GEMM_PAIR = 1024   # DTDS_GEMM_PAIR in include/dtds_b200.h
 _tune_cache: dict = {}
 _AUTOTUNE = os.environ.get("DTDS_AUTOTUNE", "1") != "0"
 
 
 def _tuned_block_n(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn, b_mn, act, out_fp32, alpha):
-    """Measured tile-width choice.  At the token counts of the reference's scripts the GEMMs have
+    """Measured tile choice (BLOCK_N 64/128/256 on one CTA, or 256 x 128/256 on a CTA pair).  At the token counts of the reference's scripts the GEMMs have
     one or two waves of tiles and are bound by L2 fill rate, launch latency and epilogue cost in
     proportions that differ per shape, so the first eager call of every distinct problem times the
     three BLOCK_N variants (CUDA events, scratch outputs) and caches the winner.  Never runs while a
@@ -118,6 +119,8 @@ def _tuned_block_n(L, a, b, out, bias, residual, pre_out, dact_in, M, N, K, a_mn
     if torch.cuda.is_current_stream_capturing():
         return 0
     cands = [bn for bn in (64, 128, 256) if bn == 64 or N > bn // 2]
+    if M > 128:   # 256 x bn tiles on CTA pairs (cta_group::2): half the B bytes per SM
+        cands += [GEMM_PAIR + bn for bn in (128, 256) if N > bn // 2]
     if len(cands) == 1:
         _tune_cache[key] = cands[0]
         return cands[0]
