@@ -125,11 +125,19 @@ def all_reduce(tensor: torch.Tensor, op=dist.ReduceOp.SUM, group=None, backend: 
     return tensor
 
 
+def _staged_ok(t: torch.Tensor) -> bool:
+    """The tensor can go through the symmetric scratch buffer and the P2P kernels."""
+    return custom_kernels_active(t) and t.is_contiguous() and not torch.cuda.is_current_stream_capturing()
+
+
 def broadcast(tensor: torch.Tensor, src: int = 0, group=None, log_name: str = "broadcast"):
     if not is_initialized() or get_world_size(group) == 1:
         return tensor
     with comms_logger.record(log_name, _nbytes(tensor), get_world_size(group), tensor):
-        dist.broadcast(tensor, src=src, group=group)
+        if _staged_ok(tensor):
+            symm_context(group).broadcast_tensor(tensor, src)
+        else:
+            dist.broadcast(tensor, src=src, group=group)
     return tensor
 
 
@@ -139,7 +147,10 @@ def reduce_scatter_tensor(output: torch.Tensor, input: torch.Tensor, group=None,
         output.copy_(input.view_as(output))
         return output
     with comms_logger.record(log_name, _nbytes(input), get_world_size(group), input):
-        if input.is_cuda:
+        if _staged_ok(input) and _staged_ok(output) and input.dtype in (torch.bfloat16, torch.float32, torch.int64) \
+                and _nbytes(output) % 16 == 0:
+            symm_context(group).reduce_scatter_tensor(output, input)
+        elif input.is_cuda:
             dist.reduce_scatter_tensor(output, input, group=group)
         else:  # gloo has no reduce_scatter: all-reduce a copy and slice
             tmp = input.clone()
@@ -155,7 +166,9 @@ def all_gather_into_tensor(output: torch.Tensor, input: torch.Tensor, group=None
         output.view(-1)[:input.numel()].copy_(input.view(-1))
         return output
     with comms_logger.record(log_name, _nbytes(output), get_world_size(group), input):
-        if input.is_cuda:
+        if _staged_ok(input) and _staged_ok(output) and _nbytes(input) % 16 == 0:
+            symm_context(group).all_gather_tensor(output, input)
+        elif input.is_cuda:
             dist.all_gather_into_tensor(output, input, group=group)
         else:
             parts = list(output.view(get_world_size(group), -1).unbind(0))

@@ -141,6 +141,17 @@ class SymmContext:
                   per_rank_elems: int, master, m, v, step, lr, beta1, beta2, eps, weight_decay,
                   grad_scale=1.0, adamw_mode=True, bias_correction=True, param_shard=None,
                   push_params=True, blocks: int = 0):
+        gmc = int(getattr(grads, "mc_ptr", 0) or 0)
+        pmc = int(getattr(params, "mc_ptr", 0) or 0) if params is not None else 0
+        if gmc or pmc:   # in-switch reduction of the gradient slice / replication of the updated slice
+            rc = _lib.lib().dtds_zero_step_nvls(
+                grads.ptr_array, self.signal.ptr_array, params.ptr_array if params is not None else None,
+                self.rank, self.world, int(goff_elems), int(poff_elems), int(per_rank_elems),
+                master.data_ptr(), m.data_ptr(), v.data_ptr(), _lib.ptr(param_shard), step.data_ptr(),
+                float(lr), float(beta1), float(beta2), float(eps), float(weight_decay), float(grad_scale),
+                int(adamw_mode), int(bias_correction), int(push_params), int(blocks), gmc, pmc, _lib.stream_ptr())
+            _lib.check(rc, "dtds_zero_step_nvls")
+            return
         rc = _lib.lib().dtds_zero_step(
             grads.ptr_array, self.signal.ptr_array, params.ptr_array if params is not None else None,
             self.rank, self.world, int(goff_elems), int(poff_elems), int(per_rank_elems),
@@ -169,17 +180,61 @@ class SymmContext:
         return t
 
 
+def _staged_methods():
+    """reduce-scatter / all-gather / broadcast for tensors outside symmetric memory, staged through the
+    context's symmetric scratch buffer (the P2P kernels need peer-mapped operands)."""
+
+    def reduce_scatter_tensor(self, output: torch.Tensor, input: torch.Tensor):
+        nb = input.numel() * input.element_size()
+        per = nb // self.world
+        assert per * self.world == nb and per % 16 == 0 and output.numel() * output.element_size() == per
+        sc = self.scratch(nb)
+        sc.tensor(torch.uint8, nb).copy_(input.view(torch.uint8).reshape(-1))
+        self.reduce_scatter(sc, 0, per, input.dtype, output)
+        return output
+
+    def all_gather_tensor(self, output: torch.Tensor, input: torch.Tensor):
+        per = input.numel() * input.element_size()
+        nb = per * self.world
+        assert per % 16 == 0 and output.numel() * output.element_size() == nb
+        sc = self.scratch(nb)
+        self.all_gather(sc, 0, per, input)     # pushes into slot `rank` of every peer's scratch
+        # the next collective on this scratch starts with a cross-GPU entry barrier, which every rank
+        # reaches (in stream order) only after this copy: no peer can refill the scratch under it
+        output.view(torch.uint8).reshape(-1).copy_(sc.tensor(torch.uint8, nb))
+        return output
+
+    def broadcast_tensor(self, t: torch.Tensor, src: int):
+        nb = t.numel() * t.element_size()
+        padded = (nb + 15) // 16 * 16
+        sc = self.scratch(padded)
+        stage = sc.tensor(torch.uint8, padded)
+        if self.rank == src:
+            stage[:nb].copy_(t.view(torch.uint8).reshape(-1))
+        self.broadcast(sc, 0, padded, root=src)
+        if self.rank != src:
+            t.view(torch.uint8).reshape(-1).copy_(stage[:nb])
+        return t
+
+    SymmContext.reduce_scatter_tensor = reduce_scatter_tensor
+    SymmContext.all_gather_tensor = all_gather_tensor
+    SymmContext.broadcast_tensor = broadcast_tensor
+
+
+_staged_methods()
+
+
 class McastBuffer:
     """Symmetric buffer that is also bound to an NVSwitch multicast object (NVLS).
 
-    Allocation, handle exchange and the cuMulticast* binding come from
-    ``torch.distributed._symmetric_memory`` (cuMem + fabric/fd handles); the kernels that use the
-    resulting addresses are ours (csrc/comm_p2p.cu: allreduce_nvls_kernel).  ``available`` is False
-    when the platform gives no multicast address (no NVSwitch, driver without NVLS): callers then
-    stay on the P2P kernels."""
+    Allocation (cuMemCreate), the exchange of shareable handles between the rank processes (file
+    descriptors over unix sockets) and the cuMulticastCreate / AddDevice / BindMem sequence are the
+    library's own (csrc/symm_mcast.cu); this class only sequences the steps over the bootstrap group.
+    ``DTDS_MC_RUNTIME=torch`` takes the buffer from ``torch.distributed._symmetric_memory`` instead
+    (also the automatic fallback if the own path fails on a platform).  ``available`` is False when
+    there is no multicast address (no NVSwitch, driver without NVLS): callers stay on the P2P kernels."""
 
     def __init__(self, nbytes: int, group=None):
-        import torch.distributed._symmetric_memory as tsm
         self.group = group
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
@@ -187,17 +242,83 @@ class McastBuffer:
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.available = False
         self.mc_ptr = 0
+        self.runtime = None
+        self.error = None
+        self._t = None
+        self._id = None
+        import os
+        want = os.environ.get("DTDS_MC_RUNTIME", "own").lower()
+        if want != "torch":
+            self._init_own()
+        if not self.available and want != "own-only":
+            self._init_torch()
+
+    # ---- own runtime ---------------------------------------------------------------------------
+    def _agree(self, ok: bool) -> bool:
+        """True only if the step succeeded on every rank (a collective: keeps ranks in lockstep)."""
+        flags = [None] * self.world
+        dist.all_gather_object(flags, bool(ok), group=self.group)
+        return all(flags)
+
+    def _init_own(self):
+        L = _lib.lib()
         try:
+            if not self._agree(bool(L.dtds_mc_supported())):
+                self.error = "multicast not supported on every device"
+                return
+            out_bytes = ctypes.c_size_t(0)
+            bid = L.dtds_mc_create(self.nbytes, self.rank, self.world, ctypes.byref(out_bytes))
+            if not self._agree(bid >= 0):
+                self.error = f"dtds_mc_create -> {bid}"
+                return
+            self._id = bid
+            import os
+            info = [None] * self.world
+            dist.all_gather_object(info, (os.getpid(), bid), group=self.group)   # sockets are bound by now
+            rc = L.dtds_mc_root_create(bid) if self.rank == 0 else 0
+            if not self._agree(rc == 0):
+                self.error = f"cuMulticastCreate -> {rc}"
+                return
+            pids = (ctypes.c_int * self.world)(*[i[0] for i in info])
+            ids = (ctypes.c_int * self.world)(*[i[1] for i in info])
+            rc = L.dtds_mc_send_fds(bid, pids, ids)
+            rc = rc or L.dtds_mc_recv_add(bid)
+            if not self._agree(rc == 0):      # also the barrier "every device has been added"
+                self.error = f"fd exchange / cuMulticastAddDevice -> {rc}"
+                return
+            ptrs = (ctypes.c_ulonglong * self.world)()
+            mc = ctypes.c_ulonglong(0)
+            rc = L.dtds_mc_bind_map(bid, ptrs, ctypes.byref(mc))
+            if not self._agree(rc == 0):      # also the barrier "every rank is bound and zero-filled"
+                self.error = f"cuMulticastBindMem / map -> {rc}"
+                return
+            self.nbytes_alloc = int(out_bytes.value)
+            self.ptrs = [int(x) for x in ptrs]
+            self.local_ptr = self.ptrs[self.rank]
+            self.ptr_array = (ctypes.c_ulonglong * self.world)(*self.ptrs)
+            self.mc_ptr = int(mc.value)
+            self._raw = _RawCudaMemory(self.local_ptr, self.nbytes)
+            self._t = torch.as_tensor(self._raw, device=self.device)
+            self.available = self.mc_ptr != 0
+            self.runtime = "own"
+        except Exception as e:  # noqa: BLE001
+            self.error = f"{type(e).__name__}: {e}"
+
+    # ---- torch runtime (fallback) --------------------------------------------------------------
+    def _init_torch(self):
+        try:
+            import torch.distributed._symmetric_memory as tsm
             self._t = tsm.empty(self.nbytes, dtype=torch.uint8, device=self.device)
-            pg = group if group is not None else dist.group.WORLD
+            pg = self.group if self.group is not None else dist.group.WORLD
             self._hdl = tsm.rendezvous(self._t, pg)
             self.mc_ptr = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
             self.ptrs = [int(p) for p in self._hdl.buffer_ptrs]
             self.local_ptr = self.ptrs[self.rank]
             self.ptr_array = (ctypes.c_ulonglong * self.world)(*self.ptrs)
             self.available = self.mc_ptr != 0
+            self.runtime = "torch"
         except Exception as e:  # noqa: BLE001
-            self.error = f"{type(e).__name__}: {e}"
+            self.error = f"{self.error}; torch: {type(e).__name__}: {e}"
             self._t = None
 
     def tensor(self, dtype: torch.dtype, numel: int | None = None, offset_bytes: int = 0) -> torch.Tensor:
@@ -205,6 +326,11 @@ class McastBuffer:
         if numel is None:
             numel = (self.nbytes - offset_bytes) // esz
         return self._t[offset_bytes:offset_bytes + numel * esz].view(dtype)
+
+    def offset_of(self, t: torch.Tensor) -> int:
+        off = t.data_ptr() - self.local_ptr
+        assert 0 <= off <= self.nbytes, "tensor does not live in this symmetric buffer"
+        return off
 
 
 def all_reduce_nvls(ctx: "SymmContext", buf: McastBuffer, offset_bytes: int, nbytes: int, dtype, *,
@@ -214,3 +340,28 @@ def all_reduce_nvls(ctx: "SymmContext", buf: McastBuffer, offset_bytes: int, nby
     rc = _lib.lib().dtds_allreduce_nvls(buf.mc_ptr, ctx.signal.ptr_array, ctx.rank, ctx.world, offset_bytes,
                                         nbytes, DTYPE_CODE[dtype], float(scale), int(blocks), _lib.stream_ptr())
     _lib.check(rc, "dtds_allreduce_nvls")
+
+
+def reduce_scatter_nvls(ctx: "SymmContext", buf: McastBuffer, offset_bytes: int, nbytes_per_rank: int, dtype,
+                        out: torch.Tensor, *, scale: float = 1.0, blocks: int = 0) -> None:
+    assert buf.available and dtype in (torch.bfloat16, torch.float32)
+    rc = _lib.lib().dtds_reduce_scatter_nvls(buf.mc_ptr, ctx.signal.ptr_array, ctx.rank, ctx.world, out.data_ptr(),
+                                             offset_bytes, nbytes_per_rank, DTYPE_CODE[dtype], float(scale),
+                                             int(blocks), _lib.stream_ptr())
+    _lib.check(rc, "dtds_reduce_scatter_nvls")
+
+
+def all_gather_nvls(ctx: "SymmContext", buf: McastBuffer, offset_bytes: int, nbytes_per_rank: int,
+                    src: torch.Tensor, *, blocks: int = 0) -> None:
+    assert buf.available
+    rc = _lib.lib().dtds_all_gather_nvls(buf.mc_ptr, ctx.signal.ptr_array, ctx.rank, ctx.world, src.data_ptr(),
+                                         offset_bytes, nbytes_per_rank, int(blocks), _lib.stream_ptr())
+    _lib.check(rc, "dtds_all_gather_nvls")
+
+
+def broadcast_nvls(ctx: "SymmContext", buf: McastBuffer, offset_bytes: int, nbytes: int, root: int = 0, *,
+                   blocks: int = 0) -> None:
+    assert buf.available
+    rc = _lib.lib().dtds_broadcast_nvls(buf.mc_ptr, buf.ptr_array, ctx.signal.ptr_array, ctx.rank, ctx.world,
+                                        int(root), offset_bytes, nbytes, int(blocks), _lib.stream_ptr())
+    _lib.check(rc, "dtds_broadcast_nvls")

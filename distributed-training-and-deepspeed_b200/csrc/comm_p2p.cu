@@ -316,6 +316,9 @@ __global__ void __launch_bounds__(kCommThreads) barrier_kernel(PeerTable pt) {
   cross_gpu_barrier(pt, 0);
 }
 
+__device__ __forceinline__ uint4 mm_ld_reduce_bf16(const char* addr);
+__device__ __forceinline__ void mm_st(char* addr, const uint4& r);
+
 // ------------------------------------------------------------------------- ZeRO step kernel
 // One launch = gradient reduce-scatter + Adam on the owned partition + parameter all-gather.
 //   grads : symmetric bf16 buffer (every rank holds its full local gradient); rank r owns elements
@@ -333,6 +336,11 @@ struct ZeroStepArgs {
   const int* step;
   float lr, beta1, beta2, eps, weight_decay, grad_scale;
   int adamw_mode, bias_correction, push_params;
+  // NVLS: multicast addresses of the gradient / parameter buffers (0 = peer loads / peer stores).
+  // With them the owned gradient slice is reduced inside the switch (one multimem.ld_reduce per
+  // 16 bytes instead of world peer loads) and the updated slice is replicated by one multimem.st.
+  const char* grads_mc;
+  char* params_mc;
 };
 
 __global__ void __launch_bounds__(kCommThreads) zero_rs_adam_ag_kernel(ZeroStepArgs a) {
@@ -351,7 +359,14 @@ __global__ void __launch_bounds__(kCommThreads) zero_rs_adam_ag_kernel(ZeroStepA
   for (size_t vi = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; vi < nvec;
        vi += static_cast<size_t>(gridDim.x) * blockDim.x) {
     float g[8];
-    reduce_vec<__nv_bfloat16>(pt, g_base + vi * 16, g);
+    if (a.grads_mc != nullptr) {
+      const uint4 r = mm_ld_reduce_bf16(a.grads_mc + g_base + vi * 16);
+      const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { g[2 * i] = bf16_lo(w[i]); g[2 * i + 1] = bf16_hi(w[i]); }
+    } else {
+      reduce_vec<__nv_bfloat16>(pt, g_base + vi * 16, g);
+    }
     float p[8], mm[8], vv[8];
     const size_t e = vi * 8;
     *reinterpret_cast<float4*>(p) = *reinterpret_cast<const float4*>(a.master + e);
@@ -379,7 +394,9 @@ __global__ void __launch_bounds__(kCommThreads) zero_rs_adam_ag_kernel(ZeroStepA
     const uint4 lp = make_uint4(pack_bf16x2(p[0], p[1]), pack_bf16x2(p[2], p[3]),
                                 pack_bf16x2(p[4], p[5]), pack_bf16x2(p[6], p[7]));
     if (a.param_shard != nullptr) *reinterpret_cast<uint4*>(a.param_shard + e) = lp;
-    if (a.push_params) {
+    if (a.push_params && a.params_mc != nullptr) {
+      mm_st(a.params_mc + p_base + vi * 16, lp);
+    } else if (a.push_params) {
 #pragma unroll 1
       for (int k = 0; k < pt.world; ++k) {
         const int peer = (pt.rank + k) % pt.world;
@@ -565,14 +582,15 @@ extern "C" int dtds_device_barrier(const unsigned long long* signal_ptrs, int ra
   return 0;
 }
 
-extern "C" int dtds_zero_step(const unsigned long long* grad_ptrs,
-                              const unsigned long long* signal_ptrs,
-                              const unsigned long long* param_ptrs, int rank, int world,
-                              size_t goff_elems, size_t poff_elems, size_t per_rank_elems,
-                              float* master, float* m, float* v, void* param_shard, const int* step,
-                              float lr, float beta1, float beta2, float eps, float weight_decay,
-                              float grad_scale, int adamw_mode, int bias_correction,
-                              int push_params, int blocks, cudaStream_t stream) {
+extern "C" int dtds_zero_step_nvls(const unsigned long long* grad_ptrs,
+                                   const unsigned long long* signal_ptrs,
+                                   const unsigned long long* param_ptrs, int rank, int world,
+                                   size_t goff_elems, size_t poff_elems, size_t per_rank_elems,
+                                   float* master, float* m, float* v, void* param_shard, const int* step,
+                                   float lr, float beta1, float beta2, float eps, float weight_decay,
+                                   float grad_scale, int adamw_mode, int bias_correction,
+                                   int push_params, int blocks, unsigned long long grads_mc,
+                                   unsigned long long params_mc, cudaStream_t stream) {
   if (per_rank_elems == 0) return 0;
   if ((per_rank_elems % 8) || (goff_elems % 8) || (poff_elems % 8)) {
     fprintf(stderr, "[dtds] zero_step: offsets and partition size must be multiples of 8 elements\n");
@@ -590,9 +608,24 @@ extern "C" int dtds_zero_step(const unsigned long long* grad_ptrs,
   a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
   a.grad_scale = grad_scale; a.adamw_mode = adamw_mode; a.bias_correction = bias_correction;
   a.push_params = push_params && param_ptrs != nullptr;
+  a.grads_mc = reinterpret_cast<const char*>(grads_mc);
+  a.params_mc = reinterpret_cast<char*>(params_mc);
   zero_rs_adam_ag_kernel<<<comm_blocks(per_rank_elems / 8, blocks), kCommThreads, 0, stream>>>(a);
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
+}
+
+extern "C" int dtds_zero_step(const unsigned long long* grad_ptrs,
+                              const unsigned long long* signal_ptrs,
+                              const unsigned long long* param_ptrs, int rank, int world,
+                              size_t goff_elems, size_t poff_elems, size_t per_rank_elems,
+                              float* master, float* m, float* v, void* param_shard, const int* step,
+                              float lr, float beta1, float beta2, float eps, float weight_decay,
+                              float grad_scale, int adamw_mode, int bias_correction,
+                              int push_params, int blocks, cudaStream_t stream) {
+  return dtds_zero_step_nvls(grad_ptrs, signal_ptrs, param_ptrs, rank, world, goff_elems, poff_elems,
+                             per_rank_elems, master, m, v, param_shard, step, lr, beta1, beta2, eps, weight_decay,
+                             grad_scale, adamw_mode, bias_correction, push_params, blocks, 0ull, 0ull, stream);
 }
 
 // ------------------------------------------------------------------------- segment gather (pull)
@@ -714,6 +747,91 @@ allreduce_nvls_kernel(PeerTable pt, char* mc, size_t off_bytes, size_t nvec, flo
 }
 }  // namespace dtds
 
+namespace dtds {
+__device__ __forceinline__ uint4 mm_ld_reduce_bf16(const char* addr) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(addr) : "memory");
+  return r;
+}
+__device__ __forceinline__ uint4 mm_ld_reduce_f32(const char* addr) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(addr) : "memory");
+  return r;
+}
+__device__ __forceinline__ void mm_st(char* addr, const uint4& r) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "r"(r.x), "r"(r.y),
+               "r"(r.z), "r"(r.w)
+               : "memory");
+}
+__device__ __forceinline__ uint4 scale_raw(uint4 r, float scale, bool bf16) {
+  if (scale == 1.f) return r;
+  if (bf16) {
+    uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) w[i] = pack_bf16x2(bf16_lo(w[i]) * scale, bf16_hi(w[i]) * scale);
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  r.x = __float_as_uint(__uint_as_float(r.x) * scale);
+  r.y = __float_as_uint(__uint_as_float(r.y) * scale);
+  r.z = __float_as_uint(__uint_as_float(r.z) * scale);
+  r.w = __float_as_uint(__uint_as_float(r.w) * scale);
+  return r;
+}
+
+// Reduce-scatter through the switch: out[0:per) = scale * sum over ranks of slice `rank` (one
+// multimem.ld_reduce per 16 bytes instead of world-1 peer loads).
+template <bool BF16>
+__global__ void __launch_bounds__(kCommThreads)
+reduce_scatter_nvls_kernel(PeerTable pt, const char* mc, void* out, size_t off_bytes, size_t nvec_per_rank,
+                           float scale) {
+  cross_gpu_barrier(pt, 0);
+  const char* base = mc + off_bytes + nvec_per_rank * pt.rank * 16;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (; v + 3 * stride < nvec_per_rank; v += 4 * stride) {
+    uint4 r[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      r[u] = BF16 ? mm_ld_reduce_bf16(base + (v + u * stride) * 16) : mm_ld_reduce_f32(base + (v + u * stride) * 16);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      *reinterpret_cast<uint4*>(static_cast<char*>(out) + (v + u * stride) * 16) = scale_raw(r[u], scale, BF16);
+  }
+  for (; v < nvec_per_rank; v += stride) {
+    const uint4 r = BF16 ? mm_ld_reduce_bf16(base + v * 16) : mm_ld_reduce_f32(base + v * 16);
+    *reinterpret_cast<uint4*>(static_cast<char*>(out) + v * 16) = scale_raw(r, scale, BF16);
+  }
+  cross_gpu_barrier(pt, 1);  // inputs may be overwritten only after every rank has read them
+}
+
+// All-gather through the switch: rank r writes its slice once (multimem.st) and the switch
+// replicates it into slot r of every rank's buffer.
+__global__ void __launch_bounds__(kCommThreads)
+all_gather_nvls_kernel(PeerTable pt, char* mc, const void* in, size_t off_bytes, size_t nvec_per_rank) {
+  cross_gpu_barrier(pt, 0);  // peers are done reading the previous contents
+  char* base = mc + off_bytes + nvec_per_rank * pt.rank * 16;
+  for (size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec_per_rank;
+       v += static_cast<size_t>(gridDim.x) * blockDim.x)
+    mm_st(base + v * 16, *reinterpret_cast<const uint4*>(static_cast<const char*>(in) + v * 16));
+  cross_gpu_barrier(pt, 1);
+}
+
+// Broadcast through the switch: the root stores its range once to the multicast address.
+__global__ void __launch_bounds__(kCommThreads)
+broadcast_nvls_kernel(PeerTable pt, char* mc, int root, size_t off_bytes, size_t nvec) {
+  cross_gpu_barrier(pt, 0);
+  if (pt.rank == root) {
+    const char* src = static_cast<const char*>(pt.data[root]) + off_bytes;
+    for (size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < nvec;
+         v += static_cast<size_t>(gridDim.x) * blockDim.x)
+      mm_st(mc + off_bytes + v * 16, *reinterpret_cast<const uint4*>(src + v * 16));
+  }
+  cross_gpu_barrier(pt, 1);
+}
+}  // namespace dtds
+
 // dtype: 0 bf16, 1 fp32.  `mc_ptr` = multicast address of the buffer (cuMulticast* binding, e.g.
 // obtained through torch.distributed._symmetric_memory), `signal_ptrs` = per-rank signal pads.
 extern "C" int dtds_allreduce_nvls(unsigned long long mc_ptr, const unsigned long long* signal_ptrs,
@@ -728,6 +846,52 @@ extern "C" int dtds_allreduce_nvls(unsigned long long mc_ptr, const unsigned lon
   char* mc = reinterpret_cast<char*>(mc_ptr);
   if (dtype == 0) dtds::allreduce_nvls_kernel<true><<<nb, dtds::kCommThreads, 0, stream>>>(pt, mc, off_bytes, nvec, scale);
   else dtds::allreduce_nvls_kernel<false><<<nb, dtds::kCommThreads, 0, stream>>>(pt, mc, off_bytes, nvec, scale);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// NVLS variants of reduce-scatter / all-gather / broadcast on a multicast-bound symmetric buffer
+// (csrc/symm_mcast.cu).  `data_ptrs` is only needed by broadcast (the root's local address).
+extern "C" int dtds_reduce_scatter_nvls(unsigned long long mc_ptr, const unsigned long long* signal_ptrs, int rank,
+                                        int world, void* out, size_t off_bytes, size_t nbytes_per_rank, int dtype,
+                                        float scale, int blocks, cudaStream_t stream) {
+  if (nbytes_per_rank == 0) return 0;
+  if ((nbytes_per_rank % 16) || (off_bytes % 16) || mc_ptr == 0 || dtype < 0 || dtype > 1) return -2;
+  dtds::PeerTable pt;
+  if (dtds::fill_table(&pt, signal_ptrs, signal_ptrs, rank, world)) return -1;
+  const size_t nvec = nbytes_per_rank / 16;
+  const int nb = dtds::comm_blocks(nvec, blocks);
+  const char* mc = reinterpret_cast<const char*>(mc_ptr);
+  if (dtype == 0) dtds::reduce_scatter_nvls_kernel<true><<<nb, dtds::kCommThreads, 0, stream>>>(pt, mc, out, off_bytes, nvec, scale);
+  else dtds::reduce_scatter_nvls_kernel<false><<<nb, dtds::kCommThreads, 0, stream>>>(pt, mc, out, off_bytes, nvec, scale);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtds_all_gather_nvls(unsigned long long mc_ptr, const unsigned long long* signal_ptrs, int rank,
+                                    int world, const void* in, size_t off_bytes, size_t nbytes_per_rank, int blocks,
+                                    cudaStream_t stream) {
+  if (nbytes_per_rank == 0) return 0;
+  if ((nbytes_per_rank % 16) || (off_bytes % 16) || mc_ptr == 0) return -2;
+  dtds::PeerTable pt;
+  if (dtds::fill_table(&pt, signal_ptrs, signal_ptrs, rank, world)) return -1;
+  const size_t nvec = nbytes_per_rank / 16;
+  dtds::all_gather_nvls_kernel<<<dtds::comm_blocks(nvec, blocks), dtds::kCommThreads, 0, stream>>>(
+      pt, reinterpret_cast<char*>(mc_ptr), in, off_bytes, nvec);
+  DTDS_HOST_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtds_broadcast_nvls(unsigned long long mc_ptr, const unsigned long long* data_ptrs,
+                                   const unsigned long long* signal_ptrs, int rank, int world, int root,
+                                   size_t off_bytes, size_t nbytes, int blocks, cudaStream_t stream) {
+  if (nbytes == 0) return 0;
+  if ((nbytes % 16) || (off_bytes % 16) || mc_ptr == 0) return -2;
+  dtds::PeerTable pt;
+  if (dtds::fill_table(&pt, data_ptrs, signal_ptrs, rank, world)) return -1;
+  const size_t nvec = nbytes / 16;
+  dtds::broadcast_nvls_kernel<<<dtds::comm_blocks(nvec, blocks), dtds::kCommThreads, 0, stream>>>(
+      pt, reinterpret_cast<char*>(mc_ptr), root, off_bytes, nvec);
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }

@@ -35,10 +35,19 @@ def grad_uses(p) -> int:
 
 
 class FlatBuffers:
+    def _try_multicast(self, nbytes, group):
+        """A multicast-bound symmetric buffer, or None unless every rank got one."""
+        from ..comm.symm import McastBuffer
+        mb = McastBuffer(nbytes, group)
+        ok = torch.tensor([1 if mb.available else 0], device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        return mb if int(ok.item()) == 1 else None
+
     def __init__(self, params, *, param_dtype: torch.dtype | None = None,
                  grad_dtype: torch.dtype | None = None, device=None, align: int = 64,
                  pad_total_to: int = 64, symmetric: bool = False, group=None,
-                 with_grads: bool = True, multicast_grads: bool = False):
+                 with_grads: bool = True, multicast_grads: bool = False,
+                 multicast_params: bool = False):
         self.params = unique_params(params)
         assert self.params, "no parameters"
         p0 = self.params[0]
@@ -62,17 +71,16 @@ class FlatBuffers:
         if self.symmetric:
             from ..comm.symm import SymmContext
             ctx = SymmContext.get(group)
-            self.param_buf = ctx.new_buffer(self.total * esz_p)
+            self.param_buf = None
+            if multicast_params:   # NVLS: updated parameter slices are replicated by the switch
+                self.param_buf = self._try_multicast(self.total * esz_p, group)
+            if self.param_buf is None:
+                self.param_buf = ctx.new_buffer(self.total * esz_p)
             self.param_flat = self.param_buf.tensor(self.param_dtype, self.total)
             if with_grads:
                 self.grad_buf = None
                 if multicast_grads:  # NVLS: gradient buffer bound to an NVSwitch multicast object
-                    from ..comm.symm import McastBuffer
-                    mb = McastBuffer(self.total * esz_g, group)
-                    ok = torch.tensor([1 if mb.available else 0], device=self.device)
-                    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
-                    if int(ok.item()) == 1:
-                        self.grad_buf = mb
+                    self.grad_buf = self._try_multicast(self.total * esz_g, group)
                 if self.grad_buf is None:
                     self.grad_buf = ctx.new_buffer(self.total * esz_g)
                 self.grad_flat = self.grad_buf.tensor(self.grad_dtype, self.total)

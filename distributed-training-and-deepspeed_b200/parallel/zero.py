@@ -160,8 +160,11 @@ class ZeroEngine(nn.Module):
         # lcm(64, 8*world): buckets split evenly over the ranks in whole 16-byte vectors for any
         # world size (3, 5, 6, 7 included), none of the tail is left unreduced
         align = math.lcm(64, 8 * self.world)
+        nvls = os.environ.get("DTDS_NVLS", "auto").lower()
+        want_mc = self.world > 1 and (nvls in ("1", "force", "on") or (nvls == "auto" and self.world >= 4))
         self.flat = FlatBuffers(params, symmetric=True, group=process_group, align=align,
-                                pad_total_to=align)
+                                pad_total_to=align, multicast_grads=want_mc,
+                                multicast_params=want_mc and self.stage < 3)
         self.lowp = self.flat.param_dtype != torch.float32
         self._custom = self.flat.symmetric and comm.custom_kernels_active(self.flat.grad_flat) \
             and self.flat.grad_dtype == torch.bfloat16

@@ -189,6 +189,40 @@ int dtds_zero_step(const unsigned long long* grad_ptrs, const unsigned long long
                    void* param_shard, const int* step, float lr, float beta1, float beta2, float eps,
                    float weight_decay, float grad_scale, int adamw_mode, int bias_correction,
                    int push_params, int blocks, cudaStream_t stream);
+/* Same kernel with the switch doing the reduction and the replication: `grads_mc` / `params_mc` are
+ * the multicast addresses of the gradient / parameter buffers (0 = peer loads / peer stores).   */
+int dtds_zero_step_nvls(const unsigned long long* grad_ptrs, const unsigned long long* signal_ptrs,
+                        const unsigned long long* param_ptrs, int rank, int world, size_t goff_elems,
+                        size_t poff_elems, size_t per_rank_elems, float* master, float* m, float* v,
+                        void* param_shard, const int* step, float lr, float beta1, float beta2,
+                        float eps, float weight_decay, float grad_scale, int adamw_mode,
+                        int bias_correction, int push_params, int blocks,
+                        unsigned long long grads_mc, unsigned long long params_mc,
+                        cudaStream_t stream);
+/* NVLS reduce-scatter (multimem.ld_reduce of the own slice), all-gather and broadcast (multimem.st:
+ * one store, the switch replicates) on a multicast-bound buffer; same contracts as the P2P ones. */
+int dtds_reduce_scatter_nvls(unsigned long long mc_ptr, const unsigned long long* signal_ptrs,
+                             int rank, int world, void* out, size_t off_bytes,
+                             size_t nbytes_per_rank, int dtype, float scale, int blocks,
+                             cudaStream_t stream);
+int dtds_all_gather_nvls(unsigned long long mc_ptr, const unsigned long long* signal_ptrs, int rank,
+                         int world, const void* in, size_t off_bytes, size_t nbytes_per_rank,
+                         int blocks, cudaStream_t stream);
+int dtds_broadcast_nvls(unsigned long long mc_ptr, const unsigned long long* data_ptrs,
+                        const unsigned long long* signal_ptrs, int rank, int world, int root,
+                        size_t off_bytes, size_t nbytes, int blocks, cudaStream_t stream);
+/* Multicast-bound symmetric buffers (csrc/symm_mcast.cu): cuMemCreate + cuMulticastCreate /
+ * AddDevice / BindMem, file descriptors passed between the rank processes over unix sockets.
+ * Call order (every rank, bootstrap barriers where noted): create -> [rank 0: root_create] ->
+ * send_fds -> recv_add -> barrier -> bind_map -> barrier.  Replaces the buffers NCCL's NVLS
+ * transport sets up internally for the reference's collectives (pytorch_allreduce.py:31).       */
+int dtds_mc_supported(void);
+int dtds_mc_create(size_t bytes, int rank, int world, size_t* bytes_out);   /* returns a buffer id */
+int dtds_mc_root_create(int id);
+int dtds_mc_send_fds(int id, const int* pids, const int* ids);
+int dtds_mc_recv_add(int id);
+int dtds_mc_bind_map(int id, unsigned long long* ptrs_out, unsigned long long* mc_ptr_out);
+int dtds_mc_free(int id);
 /* Pull-style gather: copies `nseg` byte ranges (local or peer sources) into local destinations in
  * one launch; ZeRO-3 uses it to materialise a block's parameters from the owners' shards.      */
 int dtds_copy_segments(const unsigned long long* src_ptrs, const unsigned long long* dst_ptrs,

@@ -108,6 +108,96 @@ def zero_step_matches_reference(rank, world):
         assert own < 2e-3, f"iter {it}: master partition differs by {own}"
 
 
+def nvls_collectives(rank, world, runtime="own-only"):
+    """Buffers bound to a multicast object by the library's own runtime (cuMem + cuMulticast, fds over
+    unix sockets): multimem all-reduce / reduce-scatter / all-gather / broadcast and the ZeRO step
+    kernel with in-switch reduction, against torch.distributed / the fp32 reference."""
+    import os
+    os.environ["DTDS_MC_RUNTIME"] = runtime
+    from dtds_b200 import comm
+    from dtds_b200.comm import symm
+    from dtds_b200.ops import reference as ref
+    dev = _dev(rank)
+    ctx = comm.symm_context()
+    n_per = 8192 + 64
+    n = n_per * world
+    buf = symm.McastBuffer(n * 4, None)
+    assert buf.available, f"multicast buffer unavailable: {buf.error}"
+    assert buf.runtime == ("own" if runtime.startswith("own") else "torch"), buf.runtime
+    # all-reduce (fp32 and bf16)
+    t = buf.tensor(torch.float32, n)
+    torch.manual_seed(50 + rank)
+    x = torch.randn(n, device=dev)
+    t.copy_(x)
+    want = x.clone(); dist.all_reduce(want)
+    torch.cuda.synchronize(); dist.barrier()
+    symm.all_reduce_nvls(ctx, buf, 0, n * 4, torch.float32, scale=0.5)
+    torch.cuda.synchronize()
+    assert torch.allclose(t, want * 0.5, atol=1e-5, rtol=1e-5), "nvls all_reduce fp32"
+    # reduce-scatter
+    t.copy_(torch.arange(n, device=dev, dtype=torch.float32) * (rank + 1))
+    torch.cuda.synchronize(); dist.barrier()
+    out = torch.empty(n_per, device=dev)
+    symm.reduce_scatter_nvls(ctx, buf, 0, n_per * 4, torch.float32, out, scale=0.5)
+    tot = sum(r + 1 for r in range(world))
+    want = torch.arange(rank * n_per, (rank + 1) * n_per, device=dev, dtype=torch.float32) * tot * 0.5
+    torch.cuda.synchronize()
+    assert torch.allclose(out, want), "nvls reduce_scatter"
+    # all-gather
+    src = torch.full((n_per,), float(rank + 1), device=dev)
+    symm.all_gather_nvls(ctx, buf, 0, n_per * 4, src)
+    torch.cuda.synchronize()
+    for r in range(world):
+        assert torch.all(t[r * n_per:(r + 1) * n_per] == r + 1), "nvls all_gather"
+    # broadcast
+    t.fill_(float(rank + 7))
+    torch.cuda.synchronize(); dist.barrier()
+    symm.broadcast_nvls(ctx, buf, 0, n * 4, root=world - 1)
+    torch.cuda.synchronize()
+    assert torch.all(t == world - 1 + 7), "nvls broadcast"
+    # ZeRO step with the switch reducing the gradient slice and replicating the updated slice
+    per = 8 * 1024
+    m_n = per * world
+    gbuf, pbuf = symm.McastBuffer(m_n * 2, None), symm.McastBuffer(m_n * 2, None)
+    assert gbuf.available and pbuf.available
+    g, p = gbuf.tensor(torch.bfloat16, m_n), pbuf.tensor(torch.bfloat16, m_n)
+    torch.manual_seed(7)
+    p.copy_(torch.randn(m_n, device=dev))
+    master = p.float()[rank * per:(rank + 1) * per].clone()
+    m, v = torch.zeros(per, device=dev), torch.zeros(per, device=dev)
+    step = torch.zeros((), dtype=torch.int32, device=dev)
+    ref_p, ref_m, ref_v = p.float().clone(), torch.zeros(m_n, device=dev), torch.zeros(m_n, device=dev)
+    for it in range(3):
+        torch.manual_seed(1000 + 10 * it + rank)
+        g.copy_(torch.randn(m_n, device=dev))
+        gsum = g.float().clone(); dist.all_reduce(gsum)
+        torch.cuda.synchronize(); dist.barrier()
+        ctx.zero_step(gbuf, pbuf, goff_elems=0, poff_elems=0, per_rank_elems=per, master=master, m=m, v=v,
+                      step=step, lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, grad_scale=1.0 / world)
+        step += 1
+        ref.adam_step(ref_p, gsum / world, ref_m, ref_v, it + 1, lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8,
+                      weight_decay=0.0)
+        torch.cuda.synchronize(); dist.barrier()
+        err = (p.float() - ref_p).abs().max().item()
+        assert err < 2e-2, f"iter {it}: params differ by {err}"
+    # the public API on ordinary tensors goes through the custom kernels too
+    from dtds_b200.ops import _lib
+    c0 = dict(_lib.call_counts)
+    a = torch.randn(world * 1000, device=dev)
+    o = torch.empty(1000, device=dev)
+    comm.reduce_scatter_tensor(o, a)
+    w = a.clone(); dist.all_reduce(w)
+    assert torch.allclose(o, w[rank * 1000:(rank + 1) * 1000], atol=1e-4), "reduce_scatter_tensor"
+    gat = torch.empty(world * 1000, device=dev)
+    comm.all_gather_into_tensor(gat, o)
+    assert torch.allclose(gat, w, atol=1e-4), "all_gather_into_tensor"
+    b = torch.full((777,), float(rank), device=dev, dtype=torch.bfloat16)
+    comm.broadcast(b, src=world - 1)
+    assert torch.all(b == world - 1), "broadcast"
+    used = {k for k, v in _lib.call_counts.items() if v > c0.get(k, 0)}
+    assert {"dtds_reduce_scatter", "dtds_all_gather", "dtds_broadcast"} <= used, used
+
+
 # --------------------------------------------------------------------------- DDP
 def _tiny_bert(dev, dtype, seed=0, dropout=0.0):
     from dtds_b200.models import build_model, get_config

@@ -68,6 +68,10 @@ def test_pipeline_recompute_replays_dropout():
     run_distributed("pipeline_recompute_replays_dropout", world=2, backend="nccl", args=(4,), timeout=600)
 
 
+def test_nvls_collectives_own_multicast_runtime():
+    run_distributed("nvls_collectives", world=2, backend="nccl", args=("own-only",))
+
+
 def test_optimizer_built_before_ddp_wrap():
     run_distributed("optimizer_built_before_ddp_wrap", world=2, backend="nccl")
 
