@@ -43,7 +43,8 @@ from .flat import FlatBuffers
 
 
 class _ZBucket:
-    __slots__ = ("index", "lo", "hi", "per", "params", "pending", "launched", "state_off")
+    __slots__ = ("index", "lo", "hi", "per", "params", "pending", "launched", "state_off", "goff", "prev_user",
+                 "done_event")
 
     def __init__(self, index, lo, hi, world, params):
         self.index, self.lo, self.hi = index, lo, hi
@@ -52,6 +53,7 @@ class _ZBucket:
         self.per = (hi - lo) // world
         self.params, self.pending, self.launched = params, 0, False
         self.state_off = 0
+        self.goff, self.prev_user, self.done_event = lo, None, None   # stage-3 gradient arena (zero3.py)
 
 
 def _assign(params, offsets, total, cap_elems):
@@ -164,9 +166,11 @@ class ZeroEngine(nn.Module):
         want_mc = self.world > 1 and (nvls in ("1", "force", "on") or (nvls == "auto" and self.world >= 4))
         self.flat = FlatBuffers(params, symmetric=True, group=process_group, align=align,
                                 pad_total_to=align, multicast_grads=want_mc,
-                                multicast_params=want_mc and self.stage < 3)
+                                multicast_params=want_mc and self.stage < 3,
+                                with_grads=self.stage < 3)   # stage 3 keeps gradients in a small arena
+        self._want_mc = want_mc
         self.lowp = self.flat.param_dtype != torch.float32
-        self._custom = self.flat.symmetric and comm.custom_kernels_active(self.flat.grad_flat) \
+        self._custom = self.flat.symmetric and comm.custom_kernels_active(self.flat.param_flat) \
             and self.flat.grad_dtype == torch.bfloat16
         self.flat.broadcast_params(0)  # _broadcast_model (zero_dp_training.py:46, I3)
         self.optimizer = ZeroOptimizer(self, self.flat.params, lr, betas, eps, wd)
@@ -214,6 +218,27 @@ class ZeroEngine(nn.Module):
             self.master[b.state_off:b.state_off + b.per].copy_(f.param_flat[s:s + b.per])
         self.exp_avg = torch.zeros(off, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(off, dtype=torch.float32, device=dev)
+
+    def gradient_bytes(self) -> int:
+        """Bytes of gradient storage resident on this rank (stage 3: the arena, not the model size)."""
+        if self.param3 is not None:
+            return self.param3.gradient_bytes()
+        g = self.flat.grad_flat
+        return 0 if g is None else g.numel() * g.element_size()
+
+    def parameter_bytes(self) -> int:
+        """Bytes of parameter storage resident on this rank between steps (stage 3: its shards)."""
+        if self.param3 is not None:
+            return self.param3.resident_parameter_bytes()
+        return self.flat.param_flat.numel() * self.flat.param_flat.element_size()
+
+    def memory_report(self) -> dict:
+        """What this rank holds for the model between steps, in bytes (symmetric buffers included --
+        they do not show in torch's allocator statistics because the library allocates them)."""
+        free, total = torch.cuda.mem_get_info(self.device) if self.device.type == "cuda" else (0, 0)
+        return {"stage": self.stage, "world": self.world, "parameters": self.parameter_bytes(),
+                "gradients": self.gradient_bytes(), "optimizer": self.optimizer_state_bytes(),
+                "device_used": total - free}
 
     def optimizer_state_bytes(self) -> int:
         return sum(t.numel() * t.element_size() for t in (self.master, self.exp_avg, self.exp_avg_sq))
@@ -286,8 +311,12 @@ class ZeroEngine(nn.Module):
         so = b.state_off
         master, m, v = (self.master[so:so + b.per], self.exp_avg[so:so + b.per],
                         self.exp_avg_sq[so:so + b.per])
-        esz = f.grad_flat.element_size()
+        esz = torch.empty((), dtype=f.grad_dtype).element_size()
         nbytes = (b.hi - b.lo) * esz
+        # stage 3: gradients live in the manager's arena (ring of bucket-sized slots), not in a
+        # model-sized buffer
+        gbuf = self.param3.grad_buf if self.param3 is not None else f.grad_buf
+        goff = b.goff if self.param3 is not None else b.lo
         if self._custom and self.world > 1:
             cur = torch.cuda.current_stream(self.device)
             stream = self._comm_stream if overlap else cur
@@ -305,8 +334,8 @@ class ZeroEngine(nn.Module):
                 s, e = torch.cuda.Event(enable_timing=timing), torch.cuda.Event(enable_timing=timing)
                 s.record()
                 shard = self.param3.shard_view(b) if self.param3 is not None else None
-                ctx.zero_step(f.grad_buf, None if self.param3 is not None else f.param_buf,
-                              goff_elems=b.lo, poff_elems=b.lo, per_rank_elems=b.per, master=master, m=m,
+                ctx.zero_step(gbuf, None if self.param3 is not None else f.param_buf,
+                              goff_elems=goff, poff_elems=b.lo, per_rank_elems=b.per, master=master, m=m,
                               v=v, step=self.step_count, lr=lr, beta1=b1, beta2=b2, eps=eps,
                               weight_decay=wd, grad_scale=1.0 / self.world, adamw_mode=self.adamw_mode,
                               param_shard=shard, push_params=self.param3 is None)
@@ -315,9 +344,11 @@ class ZeroEngine(nn.Module):
                 comm.comms_logger.record_events("zero_step(rs+adam+ag)", nbytes, self.world, s, e)
             if overlap:
                 self._last_event = e
+            if self.param3 is not None:
+                b.done_event = e   # the slot may be refilled only after this kernel (see zero3.py)
             return
         # ---- library path: reduce-scatter, flat Adam on the owned slice, all-gather
-        g_bucket = f.grad_flat[b.lo:b.hi]
+        g_bucket = self.param3.grad_view(b) if self.param3 is not None else f.grad_flat[b.lo:b.hi]
         if self.world > 1:
             g_own = torch.empty(b.per, dtype=g_bucket.dtype, device=self.device)
             comm.reduce_scatter_tensor(g_own, g_bucket, group=self.group)

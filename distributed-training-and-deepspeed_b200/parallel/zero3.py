@@ -55,6 +55,7 @@ class Zero3ParamManager:
             self.shard_buf = None
             self.shards = torch.empty(total_own, dtype=f.param_dtype, device=self.dev)
         self.refresh_shards_from_full()
+        self.grad_buf = self.grads = None   # set by _build_gradient_arena once the blocks are known
         # ---- blocks
         root = engine.module
         self.blocks: list[_Block] = []
@@ -83,6 +84,7 @@ class Zero3ParamManager:
                 b = bucket_of[id(p)]
                 seen[b.index] = b
             blk.buckets = list(seen.values())
+        self._build_gradient_arena()
         # all-gather fused with the first consuming GEMM: one flagged Linear weight per block
         self.fuse_gather = self.custom and bool(engine.config.get("zero_optimization", {}).get(
             "fuse_allgather_gemm", True))
@@ -110,6 +112,62 @@ class Zero3ParamManager:
             comm.barrier(engine.group)  # every rank's shards are in place before anyone pulls
 
     # ------------------------------------------------------------------------------------
+    def _build_gradient_arena(self) -> None:
+        """Stage 3 shards the gradients too (DeepSpeed stage 3, zero_dp_training.py:41 `--stage 3`):
+        a bucket's gradients are dead once its reduce-scatter + Adam kernel has run, which happens
+        right behind the backward of the block that produced them.  So instead of a model-sized
+        buffer the gradients live in an arena of `grad_ring_buckets` bucket-sized slots that the
+        buckets take turns using in backward order, plus fixed space for the buckets of parameters
+        that collect gradients over the whole backward (tied embeddings).  A slot is refilled only
+        after the previous user's kernel has completed (event wait in the block's pre-backward hook)."""
+        e, f = self.e, self.flat
+        zcfg = e.config.get("zero_optimization", {}) or {}
+        depth = max(2, int(zcfg.get("grad_ring_buckets", 4)))
+        pinned_ids = {id(p) for p in self.pinned.params}
+        ring = [b for b in e.buckets if not any(id(p) in pinned_ids for p in b.params)]
+        fixed = [b for b in e.buckets if any(id(p) in pinned_ids for p in b.params)]
+        slot = max((b.hi - b.lo for b in ring), default=0)
+        slots = min(depth, len(ring))
+        off = 0
+        for b in fixed:
+            b.goff, b.prev_user = off, None
+            off += b.hi - b.lo
+        base = off
+        for i, b in enumerate(ring):   # e.buckets is in backward order (last parameters first)
+            b.goff = base + (i % slots) * slot
+            b.prev_user = ring[i - slots] if i >= slots else None
+        total = base + slots * slot
+        esz = torch.empty((), dtype=f.grad_dtype).element_size()
+        if self.custom and f.grad_dtype == torch.bfloat16:
+            buf = f._try_multicast(total * esz, e.group) if getattr(e, "_want_mc", False) else None
+            self.grad_buf = buf if buf is not None else comm.symm_context(e.group).new_buffer(total * esz)
+            self.grads = self.grad_buf.tensor(f.grad_dtype, total)
+        else:
+            self.grads = torch.zeros(total, dtype=f.grad_dtype, device=self.dev)
+        for b in e.buckets:
+            for p in b.params:
+                o = b.goff + (p._flat_offset - b.lo)
+                p.main_grad = self.grads[o:o + p._numel].view(p._orig_shape)
+        f.grad_flat = f.grad_buf = None
+
+    def grad_view(self, b) -> torch.Tensor:
+        return self.grads[b.goff:b.goff + (b.hi - b.lo)]
+
+    def gradient_bytes(self) -> int:
+        return self.grads.numel() * self.grads.element_size()
+
+    def _wait_slots(self, blk) -> None:
+        """Before a block's backward writes gradients: the ring slots of its buckets must have been
+        drained by their previous users (stream-ordered; the weight-gradient side stream forks from
+        the current stream after this point)."""
+        if self.dev.type != "cuda":
+            return
+        cur = torch.cuda.current_stream(self.dev)
+        for b in blk.buckets:
+            prev = b.prev_user
+            if prev is not None and prev.done_event is not None:
+                cur.wait_event(prev.done_event)
+
     def shard_view(self, b) -> torch.Tensor:
         return self.shards[b.state_off:b.state_off + b.per]
 
@@ -240,6 +298,7 @@ class Zero3ParamManager:
 
     def _pre_bwd(self, blk, idx):
         def hook(module, grad_output):
+            self._wait_slots(blk)
             self._materialize(blk)
             self._prefetch(idx - 1)
         return hook

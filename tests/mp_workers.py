@@ -361,7 +361,8 @@ def _ds_config(stage, bf16):
     return {"train_micro_batch_size_per_gpu": 2,
             "optimizer": {"type": "Adam", "params": {"lr": 1e-3}},
             "comms_logger": {"enabled": True, "verbose": False, "prof_all": True, "debug": False},
-            "zero_optimization": {"stage": stage, "reduce_bucket_size": 2e5},
+            # small buckets and a 2-slot gradient ring: stage 3 reuses every slot several times per step
+            "zero_optimization": {"stage": stage, "reduce_bucket_size": 3e4, "grad_ring_buckets": 2},
             "bf16": {"enabled": bf16}}
 
 
@@ -400,6 +401,12 @@ def zero_stages_match_stage0(rank, world, arch="bloom-tiny"):
             assert _lib.call_counts.get("dtds_gemm_bf16_allgather", 0) > 0, "fused all-gather GEMM was not used"
             assert _lib.call_counts.get("dtds_zero_step", 0) > 0, "fused RS+Adam kernel was not used"
         if stage == 3:
+            ring = [b for b in engine.buckets if b.prev_user is not None]
+            assert ring, "the gradient ring was never reused: test does not cover slot hand-over"
+            n_elems = sum(p._numel for p in engine.flat.params)
+            pinned = sum(b.hi - b.lo for b in engine.buckets if b.prev_user is None and b.goff < ring[0].goff)
+            assert engine.gradient_bytes() < (n_elems * 0.8 + pinned) * (2 if bf16 else 4), \
+                ("stage-3 gradients are not sharded", engine.gradient_bytes(), n_elems)
             assert engine.param3.resident_parameter_bytes() * world <= \
                 sum(p._numel for p in engine.flat.params) * (2 if bf16 else 4) * 1.2 + 65536 * world
     for stage in (1, 2, 3):

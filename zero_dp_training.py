@@ -72,6 +72,12 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
     print(f"Device {rank} - Optimizer: lr={group['lr']}; betas={group['betas']}; eps={group['eps']}; "
           f"parameter count={sum(p._numel for p in group['params']):,}")
 
+    if rank == 0:
+        rep = model_engine.memory_report()
+        gb = 1024 ** 3
+        print(f"Device {rank} - ZeRO-{stage} resident model state per rank ({world_size} rank(s)): "
+              f"parameters {rep['parameters'] / gb:.3f} GB, gradients {rep['gradients'] / gb:.3f} GB, "
+              f"optimizer {rep['optimizer'] / gb:.3f} GB; device memory in use {rep['device_used'] / gb:.2f} GB")
     tokenizer = synthetic_tokenizer(cfg)
     collator = synthetic_collator(tokenizer, mlm=False)
     seq = min(seq_len, cfg.max_position_embeddings)
@@ -100,7 +106,11 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
         if rank == 0:
             print(f"Resumed from {resume} at step {start_step}")
     graphed = None
-    use_graph = cuda_graph and on_gpu and stage < 3   # stage 3 re-points parameter storage per block
+    # The whole step (forward, backward, side-stream bucket kernels, optimizer) is replayed as one CUDA
+    # graph.  Collectives inside a replay cannot be timed one by one: the comm table below then
+    # holds the eager warm-up steps before the capture.  Stage 3 (per-block parameter gathers
+    # driven by module hooks) is captured when DTDS_ZERO3_GRAPH=1.
+    use_graph = cuda_graph and on_gpu and (stage < 3 or os.environ.get("DTDS_ZERO3_GRAPH", "0") == "1")
     steady_start, steady_from = None, 3
     for step_idx, batch in enumerate(train_dataloader):
         if step_idx < start_step:
@@ -158,7 +168,10 @@ if __name__ == "__main__":
     parser.add_argument("--seq-len", type=int, default=512)
     parser.add_argument("--fp32", action="store_true", help="keep fp32 parameters (library collectives)")
     parser.add_argument("--quiet", action="store_true", help="no per-step MEMSTATS / progress bar")
-    parser.add_argument("--cuda-graph", action="store_true", help="replay the step as one CUDA graph (stages 0-2)")
+    parser.add_argument("--cuda-graph", dest="cuda_graph", action="store_true", default=True,
+                        help="replay the step as one CUDA graph (default on a GPU)")
+    parser.add_argument("--no-cuda-graph", dest="cuda_graph", action="store_false",
+                        help="launch every kernel eagerly (every collective is then timed in the comm table)")
     parser.add_argument("--save-dir", type=str, default=None, help="write a checkpoint here after the last step")
     parser.add_argument("--resume", type=str, default=None, help="checkpoint directory to continue from")
     parser.add_argument("--data", type=str, default=None,
