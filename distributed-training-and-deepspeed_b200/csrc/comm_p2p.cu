@@ -79,11 +79,19 @@ __device__ __forceinline__ void cross_gpu_barrier(const PeerTable& pt, int slot)
     st_release_sys(pt.signal[peer] + cell * kMaxRanks + pt.rank, e);
     const uint32_t* mine = pt.signal[pt.rank] + cell * kMaxRanks + peer;
     uint32_t spins = 0;
+    unsigned long long t_start = 0;
     while (static_cast<int32_t>(ld_acquire_sys(mine) - e) < 0) {
-      if (++spins > DTDS_SPIN_LIMIT) {
+      // bounded by wall time (60 s), not by iteration count: a peer that died must surface as an
+      // error on the survivors soon, a peer that is merely late (host jitter) must not
+      if ((++spins & 0x3FF) == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (t_start == 0) t_start = now;
+      if (now - t_start > 60000000000ull) {
         printf("[dtds] comm: barrier slot %d block %d: rank %d never saw epoch %u from rank %d\n", slot,
                blockIdx.x, pt.rank, e, peer);
         __trap();
+      }
       }
     }
   }
