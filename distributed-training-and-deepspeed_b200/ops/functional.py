@@ -52,6 +52,30 @@ def set_seed_state(state: tuple) -> None:
     _base_seed, _seed_counter = state
 
 
+def checkpoint(fn, *args):
+    """torch.utils.checkpoint (non-reentrant) for code built on the fused ops.  The fused kernels draw
+    dropout masks from the host-side seed stream above, which torch's checkpoint neither saves nor
+    restores; the backward nodes of the first run keep their seeds, so the recomputation must
+    regenerate exactly the same masks: it replays the stream from the position the first run
+    started at and then puts the stream back where it was."""
+    from torch.utils.checkpoint import checkpoint as _ckpt
+    start = get_seed_state()
+    first = [True]
+
+    def run(*a):
+        if first[0]:
+            first[0] = False
+            return fn(*a)
+        here = get_seed_state()
+        set_seed_state(start)
+        try:
+            return fn(*a)
+        finally:
+            set_seed_state(here)
+
+    return _ckpt(run, *args, use_reentrant=False)
+
+
 # ------------------------------------------------------------------ gradient emission helpers
 def grad_target(param):
     """(buffer, accumulate) for a parameter that owns a flat-buffer gradient view, else (None, _)."""
@@ -104,7 +128,13 @@ class _OnSideStream:
         # gradients written from several places (tied embeddings) stay on the main stream so the
         # overwrite-then-accumulate order of their producers is the program order
         shared = any(p is not None and getattr(p, "_grad_uses", 1) > 1 for p in params)
-        self.active = _WGRAD_SIDE and bool(self.tensors) and not shared
+        # Only gradients written in place into a flat buffer (main_grad) may be produced here: the
+        # engines / optimizers order their consumers after this stream.  A gradient handed back to
+        # autograd as a tensor would be accumulated into .grad on the main stream with nothing
+        # ordering that add after the side-stream GEMM.
+        in_place = all(p is None or not p.requires_grad or getattr(p, "main_grad", None) is not None
+                       for p in params)
+        self.active = _WGRAD_SIDE and bool(self.tensors) and not shared and in_place
 
     def __enter__(self):
         if not self.active:

@@ -23,7 +23,6 @@ import time
 
 import torch
 import torch.distributed as dist
-from torch.utils.checkpoint import checkpoint as _checkpoint
 
 from ..ops import functional as F
 from ..utils import trace as _trace
@@ -126,26 +125,7 @@ class PipelineStage:
     def _forward(self, x, mb: int, n_mb: int):
         recompute = self.checkpoint == "always" or (self.checkpoint == "except_last" and mb < n_mb - 1)
         if recompute and n_mb > 1 and torch.is_grad_enabled() and not self.is_first:
-            # The fused kernels draw dropout masks from a host-side seed stream that
-            # torch.utils.checkpoint knows nothing about.  The backward nodes created by the
-            # recomputation must regenerate exactly the masks of the first run (its output has
-            # already gone downstream), so the recomputation replays the stream from the position
-            # the first run started at and then puts the stream back where it was.
-            start = F.get_seed_state()
-            first = [True]
-
-            def run(inp):
-                if first[0]:
-                    first[0] = False
-                    return self._run(inp)
-                here = F.get_seed_state()
-                F.set_seed_state(start)
-                try:
-                    return self._run(inp)
-                finally:
-                    F.set_seed_state(here)
-
-            return _checkpoint(run, x, use_reentrant=False)
+            return F.checkpoint(self._run, x)   # replays the fused-dropout seed stream in the recomputation
         return self._run(x)
 
     def _irecv(self, shape, src):
