@@ -132,6 +132,10 @@ class DistributedDataParallel(nn.Module):
         self.expose_grads = True
         self._in_backward = False
         self._comm_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+        # per-bucket Adam (fuse_optimizer) runs on its own stream behind the bucket's all-reduce, so
+        # the update of bucket k overlaps the all-reduce of bucket k+1
+        self._opt_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+        self._opt_event = None
         self._events = []
         for i, p in enumerate(self.flat.params):
             p._on_grad_ready = self._param_ready
@@ -287,6 +291,11 @@ class DistributedDataParallel(nn.Module):
             self._comm_stream.wait_event(ready)
             self._wait_wgrad_stream(self._comm_stream, cur)
             ctx = comm.symm_context(self.group)
+            # The last buckets of a step (the embedding tables and the first layer) become ready when
+            # backward has almost no GEMMs left to hide them behind: they get the wide, bandwidth-
+            # oriented launch (one block per SM, two vectors in flight per thread).  Earlier buckets
+            # use the 64-register variant on 32 SMs' worth of blocks next to the resident GEMM CTAs.
+            tail = b.index >= len(self.buckets) - 2
             with torch.cuda.stream(self._comm_stream):
                 s = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
                 e = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
@@ -295,17 +304,24 @@ class DistributedDataParallel(nn.Module):
                     # in-switch reduction: multimem.ld_reduce + multimem.st (csrc/comm_p2p.cu)
                     from ..comm.symm import all_reduce_nvls
                     all_reduce_nvls(ctx, self.flat.grad_buf, b.lo * esz, nbytes, g.dtype,
-                                    scale=1.0 / self.world, blocks=self.comm_blocks or 32)
+                                    scale=1.0 / self.world, blocks=self.comm_blocks or (96 if tail else 32))
+                elif tail and not self.comm_blocks:
+                    ctx.all_reduce(self.flat.grad_buf, b.lo * esz, nbytes, g.dtype, scale=1.0 / self.world,
+                                   algo=2, blocks=128)
                 else:
                     ctx.all_reduce(self.flat.grad_buf, b.lo * esz, nbytes, g.dtype, scale=1.0 / self.world,
                                    algo=3, blocks=self.comm_blocks)
                 e.record()
             comm.comms_logger.record_events("all_reduce", nbytes, self.world, s, e)
-            self._step_bucket(b, self._comm_stream)
-            if self.optimizer is not None:
-                e = torch.cuda.Event()
-                e.record(self._comm_stream)
             self._events.append(e)
+            if self.optimizer is not None and not self._accumulating:
+                if b.sparse_pending:
+                    self._step_bucket(b, self._comm_stream)    # deferred until the lookup rows are in
+                else:
+                    self._opt_stream.wait_event(e)
+                    self._step_bucket(b, self._opt_stream)
+                    self._opt_event = torch.cuda.Event()
+                    self._opt_event.record(self._opt_stream)
         else:
             view = g[b.lo:b.hi]
             comm.all_reduce(view, group=self.group, backend="nccl", scale=1.0 / self.world)
@@ -339,6 +355,9 @@ class DistributedDataParallel(nn.Module):
             if self._custom and self._events:
                 cur = torch.cuda.current_stream(self.device)
                 cur.wait_event(self._events[-1])
+                if self._opt_event is not None:
+                    cur.wait_event(self._opt_event)
+                    self._opt_event = None
             if self.expose_grads and self.flat.grad_dtype == self.flat.param_dtype:
                 for p in self.flat.params:  # torch-style optimizers read p.grad
                     p.grad = p.main_grad
