@@ -410,18 +410,25 @@ extern "C" int dtds_embedding_bwd_sorted(const long long* sorted_ids, const long
   return 0;
 }
 
-extern "C" int dtds_cross_entropy(const void* logits, const long long* labels, void* dlogits,
-                                  float* stats /* [2], zeroed by this call */, float* row_loss,
-                                  int rows, int vocab, int ld, int seq, int shift,
-                                  long long ignore_index, float gscale, cudaStream_t stream) {
+// `n_valid_dev` (optional, one float on the device): normalise by this count instead of the
+// number of non-ignored labels among `rows` -- a micro-batch of a pipelined batch divides by the
+// whole batch's count, so the micro-batch losses simply add up and no count travels to the host.
+extern "C" int dtds_cross_entropy_ex(const void* logits, const long long* labels, void* dlogits,
+                                     float* stats /* [2], written by this call */, float* row_loss,
+                                     int rows, int vocab, int ld, int seq, int shift,
+                                     long long ignore_index, float gscale, const float* n_valid_dev,
+                                     cudaStream_t stream) {
   if (rows <= 0) return 0;
   if (ld % 8 != 0) {
     fprintf(stderr, "[dtds] cross_entropy: ld (%d) must be a multiple of 8\n", ld);
     return -1;
   }
   DTDS_HOST_CHECK(cudaMemsetAsync(stats, 0, 2 * sizeof(float), stream));
-  ce_count_kernel<<<8, 256, 0, stream>>>(reinterpret_cast<const int64_t*>(labels), rows, seq, shift,
-                                         ignore_index, stats);
+  if (n_valid_dev != nullptr)
+    DTDS_HOST_CHECK(cudaMemcpyAsync(stats, n_valid_dev, sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  else
+    ce_count_kernel<<<8, 256, 0, stream>>>(reinterpret_cast<const int64_t*>(labels), rows, seq, shift,
+                                           ignore_index, stats);
   DTDS_HOST_CHECK(cudaGetLastError());
   ce_fwd_bwd_kernel<<<rows, kCeThreads, 0, stream>>>(
       static_cast<const __nv_bfloat16*>(logits), reinterpret_cast<const int64_t*>(labels),
@@ -429,6 +436,14 @@ extern "C" int dtds_cross_entropy(const void* logits, const long long* labels, v
       ignore_index, gscale);
   DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
+}
+
+extern "C" int dtds_cross_entropy(const void* logits, const long long* labels, void* dlogits,
+                                  float* stats /* [2], zeroed by this call */, float* row_loss,
+                                  int rows, int vocab, int ld, int seq, int shift,
+                                  long long ignore_index, float gscale, cudaStream_t stream) {
+  return dtds_cross_entropy_ex(logits, labels, dlogits, stats, row_loss, rows, vocab, ld, seq, shift,
+                               ignore_index, gscale, nullptr, stream);
 }
 
 extern "C" int dtds_adam_flat(float* p, void* p_lp, const void* g, float* m, float* v, size_t n,

@@ -95,13 +95,13 @@ class BertOnlyMLMHead(nn.Module):
     def hidden(self, x):
         return self.ln(self.transform(x))
 
-    def forward(self, x, labels=None, ignore_index=-100, gscale=1.0):
+    def forward(self, x, labels=None, ignore_index=-100, gscale=1.0, n_valid=None):
         """Without labels: logits [B, S, V] (a view into a buffer whose rows are padded to 64
         columns).  With labels: the fused projection + cross-entropy loss (no logits tensor is
         returned).  Both go through ``__call__`` so module hooks (ZeRO-3 materialisation, idle
         tracking) see every use of the head's parameters."""
         if labels is not None:
-            return self.loss(x, labels, ignore_index, gscale)
+            return self.loss(x, labels, ignore_index, gscale, n_valid)
         t = self.hidden(x)
         B, S, H = t.shape
         V = self.cfg.vocab_size
@@ -110,10 +110,10 @@ class BertOnlyMLMHead(nn.Module):
             return Fn.linear(t, self.weight, self.decoder_bias)
         return _PaddedLogitsFn.apply(t, self.weight, self.decoder_bias, ld)
 
-    def loss(self, x, labels, ignore_index=-100, gscale=1.0):
+    def loss(self, x, labels, ignore_index=-100, gscale=1.0, n_valid=None):
         t = self.hidden(x)
         return Fn.lm_head_loss(t, self.weight, self.decoder_bias, labels, ignore_index=ignore_index,
-                               seq=t.shape[1], gscale=gscale)
+                               seq=t.shape[1], gscale=gscale, n_valid=n_valid)
 
 
 class _PaddedLogitsFn(torch.autograd.Function):

@@ -188,9 +188,10 @@ class BertModelWithMP(nn.Module):
             mods = [self._module(i) for i in self._mine]
             if self.stage == self.device_count - 1:
                 mods = mods[:-1]  # the head runs inside the loss (fused projection + cross-entropy)
+            head_params = list(self.head.parameters()) if self.stage == self.device_count - 1 else []
             self._pipe = PipelineStage(mods, self.stage, self.device_count, self.local_device,
                                        act_dtype=self.dtype, group=self.group, chunks=self._chunks,
-                                       tracker=self.trackers[self.stage])
+                                       tracker=self.trackers[self.stage], extra_params=head_params)
         return self._pipe
 
     def forward_backward(self, input_ids, labels):
@@ -200,9 +201,9 @@ class BertModelWithMP(nn.Module):
         st = self._stage()
         B, S = input_ids.shape
 
-        def loss_fn(h, lab, w):
-            loss = self.head(h, labels=lab, gscale=w)
-            return _ValueScale.apply(loss, w)
+        def loss_fn(h, lab, n_valid):
+            # sum of the micro-batch's token losses / labelled tokens of the whole batch
+            return self.head(h, labels=lab, n_valid=n_valid)
 
         return st.forward_backward(input_ids, labels, (B, S, self.config.hidden_size), loss_fn)
 

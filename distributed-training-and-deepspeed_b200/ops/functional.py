@@ -73,7 +73,8 @@ def checkpoint(fn, *args):
         finally:
             set_seed_state(here)
 
-    return _ckpt(run, *args, use_reentrant=False)
+    # torch's own RNG is not used by the fused ops; reading it is also illegal under stream capture
+    return _ckpt(run, *args, use_reentrant=False, preserve_rng_state=False)
 
 
 # ------------------------------------------------------------------ gradient emission helpers
@@ -173,8 +174,15 @@ class _OnSideStream:
 
 
 def wgrad_side_stream(device):
-    """The side stream weight gradients of `device` are produced on (None if never used)."""
-    return _side_streams.get(device)
+    """The side stream weight gradients of `device` are produced on (None if never used, and None
+    while a CUDA graph is being captured into which that stream has not been forked yet: it then
+    holds no work of this step, and waiting on a stream outside the capture is an error)."""
+    side = _side_streams.get(device)
+    if side is not None and torch.cuda.is_current_stream_capturing():
+        with torch.cuda.stream(side):
+            if not torch.cuda.is_current_stream_capturing():
+                return None
+    return side
 
 
 def _emit(param, compute):
@@ -556,7 +564,7 @@ class LMHeadLossFn(torch.autograd.Function):
     backward is then the dgrad / wgrad / bias column-sum of the projection."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, labels, ignore_index, shift, seq, gscale):
+    def forward(ctx, x, weight, bias, labels, ignore_index, shift, seq, gscale, n_valid=None):
         x2 = x.reshape(-1, x.shape[-1])
         M, V = x2.shape[0], weight.shape[0]
         ld = (V + 63) // 64 * 64
@@ -568,7 +576,7 @@ class LMHeadLossFn(torch.autograd.Function):
         want_grad = any(ctx.needs_input_grad)
         loss, d = K.cross_entropy(buf, labels.reshape(-1), vocab=V, ignore_index=ignore_index,
                                   shift=shift, seq=seq, want_grad=want_grad, inplace_grad=True,
-                                  gscale=gscale)
+                                  gscale=gscale, n_valid=n_valid)
         ctx.save_for_backward(x2, weight, bias)
         ctx.d = d[:, :V] if d is not None else None
         ctx.in_shape = x.shape
@@ -582,12 +590,13 @@ class LMHeadLossFn(torch.autograd.Function):
         with _OnSideStream(d, x2, params=(weight, bias)):
             dw = _wgrad(d, x2, weight)
             db = _bgrad(d, bias) if bias is not None else None
-        return dx, dw, db, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None
 
 
-def lm_head_loss(x, weight, bias, labels, *, ignore_index=-100, shift=False, seq=None, gscale=1.0):
+def lm_head_loss(x, weight, bias, labels, *, ignore_index=-100, shift=False, seq=None, gscale=1.0, n_valid=None):
+    """`n_valid`: 1-element float device tensor to normalise by (default: the rows' own count)."""
     seq = seq or (x.shape[1] if x.dim() == 3 else x.shape[0])
-    return LMHeadLossFn.apply(x, weight, bias, labels, ignore_index, shift, seq, gscale)
+    return LMHeadLossFn.apply(x, weight, bias, labels, ignore_index, shift, seq, gscale, n_valid)
 
 
 class MSEFn(torch.autograd.Function):

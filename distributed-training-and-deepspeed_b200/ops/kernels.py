@@ -394,8 +394,9 @@ def embedding_bwd_deterministic(ids, rows, dword):
 
 
 def cross_entropy(logits, labels, *, vocab=None, ignore_index=-100, shift=False, seq=None,
-                  want_grad=True, inplace_grad=True, gscale=1.0):
+                  want_grad=True, inplace_grad=True, gscale=1.0, n_valid=None):
     """Mean CE over non-ignored rows of logits [R, ld] (first `vocab` columns are real).
+    `n_valid` (1-element float tensor): divide by this count instead of the rows' own count.
 
     Returns (loss scalar fp32, dlogits or None).  With inplace_grad the gradient overwrites the
     logits buffer (the logits are dead after the loss anyway)."""
@@ -408,6 +409,9 @@ def cross_entropy(logits, labels, *, vocab=None, ignore_index=-100, shift=False,
             lf = logits[:, :vocab].float().detach().requires_grad_(want_grad)
             loss, _ = ref.cross_entropy(lf, labels.reshape(-1), ignore_index=ignore_index, shift=shift,
                                         seq=seq)
+            if n_valid is not None:   # re-normalise: mean over own rows -> sum / given count
+                own = (ref.ce_valid_count(labels.reshape(-1), ignore_index, shift, seq)).to(loss.dtype)
+                loss = loss * own / n_valid.to(loss.dtype).reshape(())
             if not want_grad:
                 return loss.detach(), None
             (g,) = torch.autograd.grad(loss, lf)
@@ -421,9 +425,10 @@ def cross_entropy(logits, labels, *, vocab=None, ignore_index=-100, shift=False,
     if want_grad:
         d = logits if inplace_grad else torch.empty_strided(logits.shape, logits.stride(), dtype=logits.dtype,
                                                             device=logits.device)
-    rc = _lib.lib().dtds_cross_entropy(
+    rc = _lib.lib().dtds_cross_entropy_ex(
         logits.data_ptr(), labels.data_ptr(), _lib.ptr(d), stats.data_ptr(), None, R, vocab, ld,
-        seq, int(shift), int(ignore_index), float(gscale), _lib.stream_ptr())
+        seq, int(shift), int(ignore_index), float(gscale),
+        None if n_valid is None else n_valid.data_ptr(), _lib.stream_ptr())
     _lib.check(rc, "dtds_cross_entropy")
     return stats[1], d
 

@@ -168,6 +168,14 @@ def cross_entropy(logits, labels, *, ignore_index=-100, shift=False, seq=None):
     return F.cross_entropy(lf, lab, ignore_index=ignore_index), lab
 
 
+def ce_valid_count(labels, ignore_index=-100, shift=False, seq=None):
+    """Number of rows that count towards the mean in `cross_entropy` (0-dim tensor)."""
+    lab = labels
+    if shift:
+        lab = lab.view(-1, seq)[:, 1:]
+    return (lab != ignore_index).sum()
+
+
 def adam_step(p, g, m, v, step, *, lr, beta1, beta2, eps, weight_decay, adamw_mode=True,
               bias_correction=True, grad_scale=1.0):
     """One fp32 Adam/AdamW update in place; `step` is the 1-based step number."""

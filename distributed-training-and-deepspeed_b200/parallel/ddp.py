@@ -295,7 +295,7 @@ class DistributedDataParallel(nn.Module):
             # backward has almost no GEMMs left to hide them behind: they get the wide, bandwidth-
             # oriented launch (one block per SM, two vectors in flight per thread).  Earlier buckets
             # use the 64-register variant on 32 SMs' worth of blocks next to the resident GEMM CTAs.
-            tail = b.index >= len(self.buckets) - 2
+            tail = b.index >= len(self.buckets) - 3
             with torch.cuda.stream(self._comm_stream):
                 s = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
                 e = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)

@@ -106,7 +106,8 @@ class PipelineStage:
 
     def __init__(self, modules, stage: int, num_stages: int, device: torch.device, *, act_dtype,
                  group=None, chunks: int = 1, checkpoint: str = "except_last",
-                 tracker: IdleTracker | None = None):
+                 tracker: IdleTracker | None = None, graphs: bool | None = None, graph_warmup: int = 2,
+                 extra_params=()):
         self.modules = list(modules)
         self.stage, self.num_stages = stage, num_stages
         self.device, self.act_dtype = device, act_dtype
@@ -115,6 +116,12 @@ class PipelineStage:
         self.checkpoint = checkpoint
         self.tracker = tracker or IdleTracker(device)
         self.is_first, self.is_last = stage == 0, stage == num_stages - 1
+        if graphs is None:
+            import os
+            graphs = os.environ.get("DTDS_PIPE_GRAPHS", "1") != "0"
+        self.use_graphs, self.graph_warmup = bool(graphs), int(graph_warmup)
+        self.extra_params = list(extra_params)   # parameters used by loss_fn (the head)
+        self._graphs, self._calls = None, 0
 
     # ------------------------------------------------------------------------------------
     def _run(self, x):
@@ -135,9 +142,137 @@ class PipelineStage:
     def forward_backward(self, input_ids, labels, act_shape, loss_fn):
         """One GPipe batch.  `input_ids` is consumed by the first stage, `labels` by the last;
         `act_shape` = (batch, seq, hidden) of the full batch at stage boundaries;
-        `loss_fn(stage_output, labels_mb, weight)` -> scalar micro-batch loss already scaled so
-        that the micro-batch losses sum to the full-batch loss.  Returns that sum on the last
-        stage, None elsewhere."""
+        `loss_fn(stage_output, labels_mb, n_valid)` -> the micro-batch's share of the batch loss:
+        the sum of its token losses divided by `n_valid`, the number of labelled tokens of the WHOLE
+        batch (a 1-element float tensor on the device; nothing is read back to the host).  Returns
+        the batch loss on the last stage, None elsewhere.
+
+        With ``graphs=True`` (default on a GPU when every parameter of the stage writes its gradient
+        in place into a flat buffer) the forward and the backward of every micro-batch slot are
+        captured once as CUDA graphs after `graph_warmup` eager batches and replayed afterwards;
+        only the NCCL hand-offs stay eager.  At 4 sequences per micro-batch a stage is otherwise
+        bound by launching ~400 kernels per micro-batch from Python."""
+        if self.use_graphs and self.device.type == "cuda":
+            self._calls += 1
+            key = (tuple(act_shape), tuple(input_ids.shape) if self.is_first else None)
+            if self._graphs is None and self._calls > self.graph_warmup and self._graphable():
+                self._capture(act_shape, input_ids, labels, loss_fn, key)
+            if self._graphs is not None and self._graphs.key == key and torch.is_grad_enabled():
+                return self._replay(input_ids, labels)
+        return self._eager(input_ids, labels, act_shape, loss_fn)
+
+    # ------------------------------------------------------------------------------------ graphs
+    def _graphable(self) -> bool:
+        ps = [p for m in self.modules for p in m.parameters() if p.requires_grad]
+        ps += [p for p in self.extra_params if p.requires_grad]
+        return all(getattr(p, "main_grad", None) is not None for p in ps)
+
+    def _reset_grad_flags(self) -> None:
+        """Gradient state as after optimizer.zero_grad(): the first writer of every flat-buffer
+        gradient overwrites, later micro-batches accumulate (this gets baked into the graphs)."""
+        seen = set()
+        for m in self.modules:
+            for p in m.parameters():
+                seen.add(id(p))
+                p._grad_written = False
+                p._uses_pending = getattr(p, "_grad_uses", 1)
+        for p in self.extra_params:
+            if id(p) not in seen:
+                p._grad_written = False
+                p._uses_pending = getattr(p, "_grad_uses", 1)
+
+    def _capture(self, act_shape, input_ids, labels, loss_fn, key) -> None:
+        from types import SimpleNamespace
+        from ..ops import kernels as K
+        M, dev = self.chunks, self.device
+        B = act_shape[0]
+        mb_shape = (B // M,) + tuple(act_shape[1:])
+        g = SimpleNamespace(key=key, pool=torch.cuda.graph_pool_handle(), stream=torch.cuda.Stream(dev),
+                            seed=torch.zeros(1, dtype=torch.int64, device=dev), fwd=[None] * M, bwd=[None] * M,
+                            y=[None] * M, loss=[None] * M, gx=[None] * M, x=[], gy=[], lab=[], n_valid=None)
+        for _ in range(M):
+            if self.is_first:
+                g.x.append(torch.zeros((B // M,) + tuple(input_ids.shape[1:]), dtype=input_ids.dtype, device=dev))
+            else:
+                g.x.append(torch.zeros(mb_shape, dtype=self.act_dtype, device=dev).requires_grad_(True))
+            if self.is_last:
+                g.lab.append(torch.full((B // M,) + tuple(labels.shape[1:]), -100, dtype=labels.dtype, device=dev))
+            else:
+                g.gy.append(torch.zeros(mb_shape, dtype=self.act_dtype, device=dev))
+        if self.is_last:
+            g.n_valid = torch.ones(1, dtype=torch.float32, device=dev)
+        torch.cuda.synchronize(dev)
+        K.set_seed_offset_tensor(g.seed)   # fresh dropout masks per replay (bumped once per batch)
+        try:
+            for k in range(M):
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr, pool=g.pool, stream=g.stream):
+                    y = self._forward(g.x[k], k, M)
+                    if self.is_last:
+                        g.loss[k] = loss_fn(y, g.lab[k], g.n_valid)
+                    else:
+                        g.y[k] = y
+                g.fwd[k] = gr
+            self._reset_grad_flags()
+            for k in reversed(range(M)):
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr, pool=g.pool, stream=g.stream):
+                    if self.is_last:
+                        g.loss[k].backward()
+                    else:
+                        g.y[k].backward(g.gy[k])
+                    if not self.is_first:
+                        g.gx[k] = g.x[k].grad
+                g.bwd[k] = gr
+        finally:
+            K.set_seed_offset_tensor(None)
+        torch.cuda.synchronize(dev)
+        self._graphs = g
+
+    def _replay(self, input_ids, labels):
+        g, M, tr = self._graphs, self.chunks, self.tracker
+        prev_rank, next_rank = self.stage - 1, self.stage + 1
+        sends = []
+        with torch.no_grad():
+            g.seed.add_(1)
+            if self.is_first:
+                for k, ids in enumerate(input_ids.chunk(M)):
+                    g.x[k].copy_(ids, non_blocking=True)
+            if self.is_last:
+                lab = labels.to(self.device, non_blocking=True)
+                g.n_valid.copy_((lab != -100).sum().clamp_min(1).to(torch.float32).reshape(1))
+                for k, l in enumerate(lab.chunk(M)):
+                    g.lab[k].copy_(l)
+            # ---------------- forward
+            pending = dist.irecv(g.x[0].detach(), src=prev_rank, group=self.group) if not self.is_first else None
+            for k in range(M):
+                if pending is not None:
+                    pending.wait()
+                    pending = dist.irecv(g.x[k + 1].detach(), src=prev_rank, group=self.group) if k + 1 < M else None
+                tr.enter(f"forward pass (micro-batch {k})")
+                g.fwd[k].replay()
+                tr.leave()
+                if not self.is_last:
+                    sends.append(dist.isend(g.y[k].detach(), dst=next_rank, group=self.group))
+            # ---------------- backward, reverse order
+            pending = dist.irecv(g.gy[M - 1], src=next_rank, group=self.group) if not self.is_last else None
+            for k in reversed(range(M)):
+                if pending is not None:
+                    pending.wait()
+                    pending = dist.irecv(g.gy[k - 1], src=next_rank, group=self.group) if k > 0 else None
+                tr.enter(f"backward pass (micro-batch {k})")
+                g.bwd[k].replay()
+                tr.leave()
+                if not self.is_first:
+                    sends.append(dist.isend(g.gx[k], dst=prev_rank, group=self.group))
+            for w in sends:
+                w.wait()
+            if self.is_last:
+                return torch.stack([l.detach() for l in g.loss]).sum()
+        return None
+
+    # ------------------------------------------------------------------------------------ eager
+    def _eager(self, input_ids, labels, act_shape, loss_fn):
         M = self.chunks
         B = act_shape[0]
         assert B % M == 0, f"batch {B} is not divisible into {M} micro-batches"
@@ -147,9 +282,9 @@ class PipelineStage:
         inputs, outputs, losses, sends = [], [], [], []
         ids_mb = input_ids.chunk(M) if self.is_first else [None] * M
         lab_mb = labels.chunk(M) if self.is_last else [None] * M
-        if self.is_last:
-            valid = [(l != -100).sum().item() for l in lab_mb]  # labels arrive from the host loader
-            total_valid = max(sum(valid), 1)
+        n_valid = None
+        if self.is_last:   # stays on the device: the micro-batch losses are sum_k / n_valid
+            n_valid = (labels.to(self.device, non_blocking=True) != -100).sum().clamp_min(1).to(torch.float32).reshape(1)
         # ---------------- forward: all micro-batches
         pending = self._irecv(mb_shape, prev_rank) if not self.is_first else None
         for k in range(M):
@@ -163,8 +298,7 @@ class PipelineStage:
             tr.enter(f"forward pass (micro-batch {k})")
             y = self._forward(x, k, M)
             if self.is_last:
-                w = valid[k] / total_valid
-                losses.append(loss_fn(y, lab_mb[k].to(self.device, non_blocking=True), w))
+                losses.append(loss_fn(y, lab_mb[k].to(self.device, non_blocking=True), n_valid))
             tr.leave()
             inputs.append(x)
             if self.is_last:

@@ -115,6 +115,11 @@ int dtds_embedding_bwd_sorted(const long long* sorted_ids, const long long* perm
 int dtds_cross_entropy(const void* logits, const long long* labels, void* dlogits, float* stats,
                        float* row_loss, int rows, int vocab, int ld, int seq, int shift,
                        long long ignore_index, float gscale, cudaStream_t stream);
+/* Same with the normalising count supplied on the device (NULL = count the non-ignored labels). */
+int dtds_cross_entropy_ex(const void* logits, const long long* labels, void* dlogits, float* stats,
+                          float* row_loss, int rows, int vocab, int ld, int seq, int shift,
+                          long long ignore_index, float gscale, const float* n_valid_dev,
+                          cudaStream_t stream);
 int dtds_adam_flat(float* p, void* p_lp, const void* g, float* m, float* v, size_t n, int* step,
                    int inc_step, int grad_fp32, float lr, float beta1, float beta2, float eps,
                    float weight_decay, float grad_scale, int adamw_mode, int bias_correction,

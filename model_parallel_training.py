@@ -63,7 +63,7 @@ def run(rank, device_count, args, backend):
     last = (not distributed) or rank == device_count - 1
     training_start_time = time.time()
     progress_bar = tqdm(range(args.training_steps)) if (not args.verbose and last) else None
-    steady_start, steady_from = None, min(3, max(args.training_steps - 1, 0))
+    steady_start, steady_from = None, min(5, max(args.training_steps - 1, 0))   # eager warm-up + graph capture are over
     for step_idx, batch in enumerate(train_dataloader):
         if step_idx == steady_from:   # connection set-up, autotuning and allocator growth are over
             if torch.cuda.is_available():

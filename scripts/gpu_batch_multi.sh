@@ -16,5 +16,5 @@ TAILN=16 CUTN=160 run timeline_N$N $TR --master-port 29534 bench/step_timeline.p
 cp gpurun_out/step_timeline_N$N.txt gpurun_out/step_timeline_dense_N$N.txt 2>/dev/null
 TAILN=16 CUTN=160 run timeline_sparse_N$N $TR --master-port 29536 bench/step_timeline.py --gpus $N --sparse-embedding-grads
 TAILN=6 run zero2_graph $TR --master-port 29537 zero_dp_training.py --stage 2 --training-steps 24 --quiet
-TAILN=6 run zero3_eager $TR --master-port 29538 zero_dp_training.py --stage 3 --training-steps 24 --quiet
-DTDS_ZERO3_GRAPH=1 TAILN=6 run zero3_graph $TR --master-port 29539 zero_dp_training.py --stage 3 --training-steps 24 --quiet
+DTDS_ZERO3_GRAPH=0 TAILN=6 run zero3_eager $TR --master-port 29538 zero_dp_training.py --stage 3 --training-steps 24 --quiet
+TAILN=6 run zero3_graph $TR --master-port 29539 zero_dp_training.py --stage 3 --training-steps 24 --quiet

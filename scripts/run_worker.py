@@ -11,6 +11,14 @@ from _mp import run_distributed  # noqa: E402
 if __name__ == "__main__":
     name, world, backend = sys.argv[1], int(sys.argv[2]), sys.argv[3]
     timeout = int(sys.argv[4]) if len(sys.argv) > 4 else 120
-    args = tuple(int(a) if a.lstrip("-").isdigit() else a for a in sys.argv[5:])
+    def conv(a):
+        try:
+            return int(a)
+        except ValueError:
+            try:
+                return float(a)
+            except ValueError:
+                return a
+    args = tuple(conv(a) for a in sys.argv[5:])
     run_distributed(name, world=world, backend=backend, args=args, timeout=timeout)
     print(f"{name}: ok")

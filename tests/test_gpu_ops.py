@@ -196,8 +196,6 @@ def test_cast_roundtrip():
     assert torch.equal(back, lp.float())
 
 
-@pytest.mark.skipif(__import__("os").environ.get("DTDS_TEST_SPARSE_ROWS", "0") == "0",
-                    reason="sorted row scatter-add: written after the GPU budget was spent (set DTDS_TEST_SPARSE_ROWS=1)")
 @pytest.mark.parametrize("fp32", [False, True])
 def test_embedding_bwd_deterministic(fp32):
     """Sorted, atomics-free row scatter-add: matches index_add_ and is bit-reproducible."""

@@ -108,9 +108,10 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
     graphed = None
     # The whole step (forward, backward, side-stream bucket kernels, optimizer) is replayed as one CUDA
     # graph.  Collectives inside a replay cannot be timed one by one: the comm table below then
-    # holds the eager warm-up steps before the capture.  Stage 3 (per-block parameter gathers
-    # driven by module hooks) is captured when DTDS_ZERO3_GRAPH=1.
-    use_graph = cuda_graph and on_gpu and (stage < 3 or os.environ.get("DTDS_ZERO3_GRAPH", "0") == "1")
+    # holds the eager warm-up steps before the capture.  Stage 3 is captured too: the per-block
+    # parameter gathers the module hooks issue land in the graph with their (pool) addresses
+    # (DTDS_ZERO3_GRAPH=0 keeps stage 3 eager).
+    use_graph = cuda_graph and on_gpu and (stage < 3 or os.environ.get("DTDS_ZERO3_GRAPH", "1") != "0")
     steady_start, steady_from = None, 3
     for step_idx, batch in enumerate(train_dataloader):
         if step_idx < start_step:
