@@ -151,9 +151,15 @@ class BertModelWithMP(nn.Module):
             return self.head
         return self.encoders[idx - 1]
 
-    def to_pipeline(self, chunks: int):
-        """GPipe over the same placement with `chunks` micro-batches (model/bert_mp.py:73-89)."""
+    def to_pipeline(self, chunks: int, checkpoint: str = "never"):
+        """GPipe over the same placement with `chunks` micro-batches (model/bert_mp.py:73-89).
+        `checkpoint`: 'never' (default), 'except_last' (torch Pipe's default: recompute the forward of
+        all micro-batches but the last during backward) or 'always'.  Recomputation only buys
+        memory; at the reference's sizes a stage's activations are a few GB of 180, and on the last
+        stage the extra forwards sit on the critical path of the whole pipeline."""
         self._chunks = max(1, int(chunks))
+        self._checkpoint = checkpoint
+        self._pipe = None
         return _Pipelined(self)
 
     # ------------------------------------------------------------------ single-process mode
@@ -191,7 +197,8 @@ class BertModelWithMP(nn.Module):
             head_params = list(self.head.parameters()) if self.stage == self.device_count - 1 else []
             self._pipe = PipelineStage(mods, self.stage, self.device_count, self.local_device,
                                        act_dtype=self.dtype, group=self.group, chunks=self._chunks,
-                                       tracker=self.trackers[self.stage], extra_params=head_params)
+                                       tracker=self.trackers[self.stage], extra_params=head_params,
+                                       checkpoint=getattr(self, "_checkpoint", "never"))
         return self._pipe
 
     def forward_backward(self, input_ids, labels):

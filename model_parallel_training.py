@@ -47,7 +47,7 @@ def run(rank, device_count, args, backend):
     config = get_config({"base": "bert-base-cased", "large": "bert-large-cased", "tiny": "bert-tiny"}[args.model])
     torch.manual_seed(0)
     bert = BertModelWithMP(config=config, device_count=device_count, verbose=args.verbose)
-    model = bert.to_pipeline(chunks=args.micro_batch_count) if args.pipeline else bert
+    model = bert.to_pipeline(chunks=args.micro_batch_count, checkpoint=args.checkpoint) if args.pipeline else bert
 
     tokenizer = synthetic_tokenizer(config)
     collator = synthetic_collator(tokenizer, mlm=True)
@@ -111,6 +111,8 @@ if __name__ == "__main__":
     parser.add_argument("--training-steps", type=int, default=250)
     parser.add_argument("--device-count", type=int, default=None)
     parser.add_argument("--micro-batch-count", type=int, default=4)
+    parser.add_argument("--checkpoint", choices=["never", "except_last", "always"], default="never",
+                        help="activation recomputation in --pipeline mode (torch Pipe's default was except_last)")
     # additions (not in the reference)
     parser.add_argument("--model", choices=["base", "large", "tiny"], default="base")
     parser.add_argument("--backend", choices=["nccl", "gloo"], default=None)

@@ -466,6 +466,53 @@ def pipeline_matches_single_process(rank, world, chunks=4):
     assert set(idle.keys()) == set(range(world))
 
 
+def pipeline_graphs_match_eager(rank, world, chunks=4, checkpoint="never"):
+    """GPipe training for 6 steps with the per-micro-batch CUDA graphs (captured at step 3) ends with
+    the same parameters as 6 eager steps from the same initial state; losses agree step by step."""
+    import os
+    from dtds_b200.models import get_config
+    from dtds_b200.models.bert_mp import BertModelWithMP
+    from dtds_b200.optim import AdamW
+    dev = _dev(rank)
+    assert dev.type == "cuda"
+    cfg = get_config("bert-tiny").replace(hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0, num_hidden_layers=4)
+    B, S = 8, 128
+    g = torch.Generator().manual_seed(3)
+    batches = []
+    for _ in range(6):
+        ids = torch.randint(0, cfg.vocab_size, (B, S), generator=g)
+        labels = ids.clone()
+        labels[:, ::3] = -100
+        batches.append((ids, labels))
+
+    def train(graphs):
+        os.environ["DTDS_PIPE_GRAPHS"] = "1" if graphs else "0"
+        torch.manual_seed(0)
+        bert = BertModelWithMP(cfg, dtype=torch.bfloat16)
+        bert.train()
+        pipe = bert.to_pipeline(chunks, checkpoint=checkpoint)
+        opt = AdamW(list(bert.parameters()), lr=1e-3)
+        losses = []
+        for ids, labels in batches:
+            opt.zero_grad()
+            loss = pipe.forward_backward(ids, labels)
+            opt.step()
+            losses.append(float(loss.item()) if loss is not None else 0.0)
+        torch.cuda.synchronize()
+        st = bert._stage()
+        assert (st._graphs is not None) == graphs, "graph capture did not happen" if graphs else "unexpected capture"
+        return losses, torch.cat([p.detach().float().flatten() for p in bert.parameters()]).cpu()
+
+    l_e, p_e = train(False)
+    l_g, p_g = train(True)
+    if rank == world - 1:
+        assert l_e[-1] < l_e[0], l_e
+        for a, b in zip(l_e, l_g):
+            assert abs(a - b) < 3e-2, (l_e, l_g)
+    err = (p_e - p_g).abs().max().item()
+    assert err < 2e-2, f"parameters after 6 steps differ by {err} between eager and graph replay"
+
+
 def pipeline_recompute_replays_dropout(rank, world, chunks=4):
     """GPipe with dropout > 0: gradients with activation recomputation ('except_last') equal the
     gradients without it ('never') when both runs start from the same dropout seed state -- the

@@ -27,13 +27,6 @@ def test_ddp_matches_single_process():
     run_distributed("ddp_matches_single_process", world=2, backend="nccl")
 
 
-# The sparse-row DDP mode is off by default and its symmetric-memory path has not been on hardware
-# yet (no multi-GPU slot was left in the round that wrote it): opt in with DTDS_TEST_SPARSE_ROWS=1.
-_sparse_rows = pytest.mark.skipif(os.environ.get("DTDS_TEST_SPARSE_ROWS", "0") == "0",
-                                  reason="sparse-row DDP mode: GPU path not validated yet (set DTDS_TEST_SPARSE_ROWS=1)")
-
-
-@_sparse_rows
 def test_ddp_sparse_embedding_rows():
     run_distributed("ddp_matches_single_process", world=2, backend="nccl", args=(0.05, True))
 
@@ -48,7 +41,6 @@ def test_ddp_fused_optimizer(use_graph):
     run_distributed("ddp_training_loop", world=2, backend="nccl", args=(use_graph, True))
 
 
-@_sparse_rows
 @pytest.mark.parametrize("use_graph", [False, True])
 def test_ddp_fused_optimizer_sparse_rows(use_graph):
     run_distributed("ddp_training_loop", world=2, backend="nccl", args=(use_graph, True, True))
@@ -62,6 +54,11 @@ def test_zero_stages_match_stage0(arch):
 @pytest.mark.parametrize("chunks", [1, 4])
 def test_pipeline_matches_single_process(chunks):
     run_distributed("pipeline_matches_single_process", world=2, backend="nccl", args=(chunks,), timeout=600)
+
+
+@pytest.mark.parametrize("checkpoint", ["never", "except_last"])
+def test_pipeline_graphs_match_eager(checkpoint):
+    run_distributed("pipeline_graphs_match_eager", world=2, backend="nccl", args=(4, checkpoint), timeout=600)
 
 
 def test_pipeline_recompute_replays_dropout():
