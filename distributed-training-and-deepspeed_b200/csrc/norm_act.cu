@@ -846,7 +846,11 @@ extern "C" int dtds_mse(const void* x, const void* t, void* dx, float* loss /* z
 //
 // In host code `g_colsum_scratch` is only a handle for the symbol, not a device address, so the
 // entry point asks the runtime for the address (cudaGetSymbolAddress) once per device, with that
-// device current, and hands the returned pointer to the kernel.
+// device current, and hands the returned pointer to the kernel.  That first call also clears the
+// array with a cudaMemsetAsync on ITS stream: other streams must be ordered behind it before they
+// use the entry point.  The kernel restores the zeros it consumed before it exits, so a launch
+// that dies part-way leaves the array dirty until the process ends (nothing can repair it without
+// the set-up path, which runs once): callers should treat such a failure as fatal for this path.
 constexpr int kNoAllocMaxCols = 32768;
 constexpr int kNoAllocMaxTiles = kNoAllocMaxCols / 64;
 static __device__ __align__(256) float g_colsum_scratch[kNoAllocMaxCols + kNoAllocMaxTiles];

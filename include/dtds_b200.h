@@ -241,8 +241,13 @@ int dtds_copy_segments(const unsigned long long* src_ptrs, const unsigned long l
  * __device__ array inside the library (132 KiB on every GPU that loads it, until process exit).
  * Limits and rules: cols <= 32768 (larger -> error code -2 and a message, nothing is launched);
  * the first call on each device resolves the array's address and clears it, so make that call
- * outside any stream capture; every call uses the same array, so two calls whose kernels could
- * overlap on the GPU (different streams without ordering) race — serialise them.                */
+ * outside any stream capture -- that clear is enqueued on the FIRST call's stream only, so a second
+ * stream may use the entry point only after an event or synchronisation orders it behind that
+ * first call; every call uses the same array, so two calls whose kernels could overlap on the GPU
+ * (different streams without ordering) race -- serialise them.  The kernel re-zeroes what it
+ * touched on its way out; if a launch dies part-way (device fault, reset of a sticky error) the
+ * partial sums and arrival counters it left behind stay dirty for the life of the process and
+ * later results are undefined: treat a failed call as fatal for this entry point.               */
 int dtds_colsum_noalloc(const void* x, int rows, int cols, int ld, void* out, int out_fp32,
                         int accumulate, cudaStream_t stream);
 
