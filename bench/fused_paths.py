@@ -94,6 +94,26 @@ def main():
     add("zero bucket 5e6 elts: reduce-scatter + Adam + all-gather (one kernel)", us, 0,
         (world - 1) / world * n * 2, "gradient slice pulled from n-1 peers, updated bf16 slice pushed to n-1 peers")
 
+    gm, pm = McastBuffer(n * 2), McastBuffer(n * 2)
+    if gm.available and pm.available:
+        gm.tensor(torch.bfloat16, n).normal_()
+        us = timed(lambda: ctx.zero_step(gm, pm, goff_elems=0, poff_elems=0, per_rank_elems=per, master=master, m=m,
+                                         v=v, step=step, lr=1e-4, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0,
+                                         grad_scale=1.0 / world), flush=flush)
+        add("zero bucket 5e6 elts: NVLS reduce-scatter + Adam + NVLS all-gather (one kernel)", us, 0, n * 2 / world * (world - 1),
+            f"multimem.ld_reduce of the owned slice, multimem.st of the updated slice ({gm.runtime} multicast runtime)")
+        from dtds_b200.comm.symm import all_gather_nvls, reduce_scatter_nvls
+        out = torch.empty(per, dtype=torch.bfloat16, device=dev)
+        us = timed(lambda: reduce_scatter_nvls(ctx, gm, 0, per * 2, torch.bfloat16, out, scale=1.0 / world), flush=flush)
+        add("reduce-scatter 10 MB bf16 (NVLS multimem.ld_reduce)", us, 0, (world - 1) / world * n * 2)
+        us = timed(lambda: all_gather_nvls(ctx, pm, 0, per * 2, out), flush=flush)
+        add("all-gather 10 MB bf16 (NVLS multimem.st)", us, 0, (world - 1) / world * n * 2)
+    out = torch.empty(per, dtype=torch.bfloat16, device=dev)
+    us = timed(lambda: ctx.reduce_scatter(g, 0, per * 2, torch.bfloat16, out, scale=1.0 / world), flush=flush)
+    add("reduce-scatter 10 MB bf16 (P2P pull)", us, 0, (world - 1) / world * n * 2)
+    us = timed(lambda: ctx.all_gather(p, 0, per * 2, out), flush=flush)
+    add("all-gather 10 MB bf16 (P2P push)", us, 0, (world - 1) / world * n * 2)
+
     # ---- ZeRO-3: all-gather fused GEMM (bloom-560m shapes, batch 1 x 512 tokens per rank) -------
     for (M, N, Kd, tag) in [(512, 3072, 1024, "bloom-560m qkv"), (512, 4096, 1024, "bloom-560m h_to_4h"),
                             (2048, 12288, 4096, "6.7B-class qkv, 2048 tokens")]:
@@ -104,7 +124,8 @@ def main():
         dist.barrier()
         x = torch.randn(M, Kd, device=dev).to(torch.bfloat16)
         w_local = torch.empty(N, Kd, dtype=torch.bfloat16, device=dev)
-        spec = K.GatherSpec([(sb.ptrs[r], per_w * 2) for r in range(world)], N * Kd * 2, dev, 32, Kd * 2)
+        spec = K.GatherSpec([(sb.ptrs[r], per_w * 2) for r in range(world)], N * Kd * 2, dev, 32, Kd * 2,
+                            local_begin=rank * per_w * 2)
         out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
         us = timed(lambda: K.gemm_allgather(x, w_local, spec, out=out), flush=flush)
         us_plain = timed(lambda: K.gemm(x, w_local, out=out), flush=flush)

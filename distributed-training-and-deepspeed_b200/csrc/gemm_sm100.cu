@@ -77,6 +77,11 @@ struct GemmParams {
   unsigned int fetch_chunk;                       // bytes per chunk (multiple of 16)
   int fetch_nseg;
   int flags_on_k;                                 // flags index rows of B along K (dgrad) not N
+  // Local-first order (all-gather fused mode): tiles / k-blocks / chunks are visited cyclically
+  // starting at this rank's own shard, which needs no NVLink transfer, so the tensor pipe has work
+  // from the first microsecond while the fetch warps pull the remote shards.
+  int n_rot, k_rot;
+  unsigned chunk_rot;
 };
 
 // Spins (bounded) until flags[f0..f1] have reached `epoch`, then fences generic -> async proxy.
@@ -226,7 +231,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t ph = 0;
       for (int tile = unit; tile < num_tiles; tile += nunits) {
         const int m0 = (tile % num_m) * (kBM * CG) + static_cast<int>(crank) * kBM;
-        const int n0 = (tile / num_m) * BN;
+        int nt = tile / num_m + p.n_rot;
+        if (nt >= num_n) nt -= num_n;
+        const int n0 = nt * BN;
         const int nb0 = n0 + static_cast<int>(crank) * (BN / CG);   // first B row this CTA stages
         if (p.ready_flags != nullptr && !p.flags_on_k) {
           // All-gather fused mode: B rows [n0, n0+BN) are written by fetch warps (of any CTA of
@@ -235,7 +242,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int n_last = min(n0 + BN, p.N) - 1;
           wait_ready_flags(p.ready_flags, n0 / p.rows_per_flag, n_last / p.rows_per_flag, p.ready_epoch);
         }
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kbi = 0; kbi < num_kb; ++kbi) {
+          int kb = kbi + p.k_rot;   // k order is free: the accumulator does not care
+          if (kb >= num_kb) kb -= num_kb;
           if (p.ready_flags != nullptr && p.flags_on_k) {  // dgrad: B rows are indexed by k
             const int k_last = min(kb * kBK + kBK, p.K) - 1;
             wait_ready_flags(p.ready_flags, kb * kBK / p.rows_per_flag, k_last / p.rows_per_flag,
@@ -328,7 +337,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // thread, then publish the chunk's arrival flag with release semantics.
     const int ft = threadIdx.x - Cfg::kThreads;
     const unsigned long long nchunks = (p.fetch_total + p.fetch_chunk - 1) / p.fetch_chunk;
-    for (unsigned long long c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    for (unsigned long long ci = blockIdx.x; ci < nchunks; ci += gridDim.x) {
+      unsigned long long c = ci + p.chunk_rot;
+      if (c >= nchunks) c -= nchunks;
       const unsigned long long b0 = c * p.fetch_chunk;
       const unsigned long long b1 = min(p.fetch_total, b0 + p.fetch_chunk);
       for (int sg = 0; sg < p.fetch_nseg; ++sg) {
@@ -372,7 +383,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int it = 0;
     for (int tile = unit; tile < num_tiles; tile += nunits, ++it) {
       const int m0 = (tile % num_m) * (kBM * CG) + static_cast<int>(crank) * kBM;
-      const int n0 = (tile / num_m) * BN;
+      int nt = tile / num_m + p.n_rot;
+      if (nt >= num_n) nt -= num_n;
+      const int n0 = nt * BN;
       const int as = it & 1;
       const uint32_t aph = (it >> 1) & 1;
       mbar_wait(&tmem_full[as], aph);
@@ -627,6 +640,7 @@ struct FetchSpec {
   int nseg;
   unsigned chunk_bytes;
   int flags_on_k;
+  unsigned long long local_begin;   // byte offset of this rank's own shard inside B
 };
 
 static int gemm_impl(const void* A, const void* B, void* D, const void* bias, const void* residual,
@@ -689,6 +703,16 @@ static int gemm_impl(const void* A, const void* B, void* D, const void* bias, co
     p.fetch_total = fetch->seg_begin[fetch->nseg];
     p.fetch_chunk = fetch->chunk_bytes;
     p.flags_on_k = fetch->flags_on_k;
+    const unsigned long long row_bytes = static_cast<unsigned long long>(ldb) * 2;
+    const unsigned long long nchunks = (p.fetch_total + p.fetch_chunk - 1) / p.fetch_chunk;
+    p.chunk_rot = static_cast<unsigned>((fetch->local_begin / p.fetch_chunk) % (nchunks ? nchunks : 1));
+    if (fetch->flags_on_k) {
+      const int num_kb = (K + kBK - 1) / kBK;
+      p.k_rot = static_cast<int>((fetch->local_begin + kBK * row_bytes - 1) / (kBK * row_bytes)) % num_kb;
+    } else {
+      const int num_n = (N + bn - 1) / bn;
+      p.n_rot = static_cast<int>((fetch->local_begin + bn * row_bytes - 1) / (bn * row_bytes)) % num_n;
+    }
   }
   const bool f = fetch != nullptr;
 
@@ -746,19 +770,21 @@ extern "C" int dtds_gemm_bf16_ex(const void* A, const void* B, void* D, const vo
 // start as soon as their part of the weight has arrived and the NVLink transfer overlaps the
 // tensor-core work tile by tile.  `flags` must hold one uint32 per chunk and `epoch` must be
 // larger than any value used with these flags before (monotonic; no reset between calls).
+// `local_begin` = byte offset inside the weight of the part this rank owns itself: tiles, k-blocks
+// and chunks are visited cyclically starting there (no transfer needed for the first ones).
 extern "C" int dtds_gemm_bf16_allgather(const void* A, void* B_local, void* D, const void* bias,
                                         const void* residual, int M, int N, int K, int lda, int ldb,
                                         int ldd, int ld_res, int b_mn_major, int act, int block_n,
                                         const unsigned long long* seg_src,
                                         const unsigned long long* seg_begin, int nseg,
                                         unsigned chunk_bytes, void* flags, unsigned epoch,
-                                        cudaStream_t stream) {
+                                        unsigned long long local_begin, cudaStream_t stream) {
   const size_t row_bytes = static_cast<size_t>(ldb) * 2;
   if (chunk_bytes == 0 || chunk_bytes % row_bytes != 0) {
     fprintf(stderr, "[dtds] gemm(all-gather): chunk_bytes must be a whole number of B rows\n");
     return -7;
   }
-  FetchSpec fs{seg_src, seg_begin, nseg, chunk_bytes, b_mn_major ? 1 : 0};
+  FetchSpec fs{seg_src, seg_begin, nseg, chunk_bytes, b_mn_major ? 1 : 0, local_begin};
   const int rows_per_flag = static_cast<int>(chunk_bytes / row_bytes);
   return gemm_impl(A, B_local, D, bias, residual, nullptr, nullptr, M, N, K, lda, ldb, ldd, ld_res, 0, 0,
                    b_mn_major, act, 0, 0, 1.0f, block_n, 0, flags, epoch, rows_per_flag, &fs, stream);

@@ -564,8 +564,9 @@ class GatherSpec:
     memory; sources are addresses valid in THIS process (local or peer-mapped symmetric memory).
     ``flags`` holds one uint32 per chunk and is reused across calls with a growing ``epoch``."""
 
-    def __init__(self, segments, total_bytes, device, chunk_rows, row_bytes):
+    def __init__(self, segments, total_bytes, device, chunk_rows, row_bytes, local_begin: int = 0):
         import ctypes
+        self.local_begin = int(local_begin)   # byte offset of this rank's own shard: work starts there
         # enough chunks that every SM's fetch warps have work (>= ~2 per SM), at least 8 rows each
         n_rows = total_bytes // row_bytes
         while chunk_rows > 8 and n_rows // chunk_rows < 2 * 148:
@@ -606,6 +607,6 @@ def gemm_allgather(a, w_local, spec: GatherSpec, *, b_mn_major=False, bias=None,
         a.data_ptr(), w_local.data_ptr(), out.data_ptr(), _lib.ptr(bias), _lib.ptr(residual), M, N, K,
         a.stride(0), w_local.stride(0), out.stride(0), residual.stride(0) if residual is not None else 0,
         int(b_mn_major), int(act), int(block_n), spec.src, spec.begin, spec.nseg, spec.chunk_bytes,
-        spec.flags.data_ptr(), spec.epoch, _lib.stream_ptr())
+        spec.flags.data_ptr(), spec.epoch, int(spec.local_begin), _lib.stream_ptr())
     _lib.check(rc, "dtds_gemm_bf16_allgather")
     return out

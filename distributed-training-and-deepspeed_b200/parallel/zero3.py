@@ -254,9 +254,15 @@ class Zero3ParamManager:
                 from ..ops.kernels import GatherSpec
                 b = self.e._bucket_of[id(lead)]
                 esz = self.shards.element_size()
-                segs = [(s, nb) for s, _, nb in self._segments(b, skip[0], skip[1])]
+                pieces = self._segments(b, skip[0], skip[1])
+                segs = [(s, nb) for s, _, nb in pieces]
                 row_bytes = lead._orig_shape[1] * esz
-                lead._ag_spec = GatherSpec(segs, lead._numel * esz, self.dev, chunk_rows=32, row_bytes=row_bytes)
+                # where this rank's own slice starts inside the weight (0 if it owns none of it)
+                mine = self.shard_buf.ptrs[self.rank]
+                span = self.shards.numel() * esz
+                local_begin = next((o - (skip[0] - b.lo) * esz for s, o, nb in pieces if mine <= s < mine + span), 0)
+                lead._ag_spec = GatherSpec(segs, lead._numel * esz, self.dev, chunk_rows=32, row_bytes=row_bytes,
+                                           local_begin=max(0, local_begin))
             lead._ag_pending = True
         if stream is not None:
             blk.event = torch.cuda.Event()

@@ -58,7 +58,7 @@ int dtds_gemm_bf16_allgather(const void* A, void* B_local, void* D, const void* 
                              const void* residual, int M, int N, int K, int lda, int ldb, int ldd,
                              int ld_res, int b_mn_major, int act, int block_n,
                              const unsigned long long* seg_src, const unsigned long long* seg_begin,
-                             int nseg, unsigned chunk_bytes, void* flags, unsigned epoch,
+                             int nseg, unsigned chunk_bytes, void* flags, unsigned epoch, unsigned long long local_begin,
                              cudaStream_t stream);
 
 /* Development aid: per-CTA clock64() timeline of the GEMM kernel into buf[grid][8]; NULL = off. */

@@ -87,16 +87,22 @@ def sweep(rank, world_size, port, out_path, max_bytes):
             torch.cuda.synchronize()
             assert torch.all(mt == 1.0), "NVLS all-reduce produced a wrong result"
             row["custom_nvls_ms"] = _time_ms(lambda: all_reduce_nvls(ctx, mc, 0, size, torch.bfloat16), iters, 5)
+        # what a user's `comm.all_reduce(tensor)` costs on an ordinary tensor: staged through the
+        # symmetric scratch (copy in, kernel, copy out), reported next to the zero-copy numbers
+        staged = torch.ones(n, dtype=torch.bfloat16, device="cuda")
+        row["public_api_staged_ms"] = _time_ms(lambda: comm.all_reduce(staged), iters, 5)
         row["nccl_ms"] = _time_ms(lambda: dist.all_reduce(plain), iters, 5)
         best = min(v for k, v in row.items() if k.startswith("custom") and k.endswith("_ms"))
         f = 2 * (world_size - 1) / world_size * size / 1e6   # bus bytes / 1e6: ms -> GB/s
         row["custom_busbw_GBps"] = f / best
+        row["public_api_busbw_GBps"] = f / row["public_api_staged_ms"]
         row["nccl_busbw_GBps"] = f / row["nccl_ms"]
         results.append(row)
         if rank == 0:
             algo = min((v, k) for k, v in row.items() if k.startswith("custom") and k.endswith("_ms"))[1][7:-3]
             row["custom_algo"] = algo
             print(f"{size:>12d} B  custom[{algo:>7s}] {row['custom_busbw_GBps']:9.2f} GB/s ({best * 1e3:9.1f} us)   "
+                  f"comm.all_reduce(tensor) {row['public_api_busbw_GBps']:9.2f} GB/s   "
                   f"nccl {row['nccl_busbw_GBps']:9.2f} GB/s ({row['nccl_ms'] * 1e3:9.1f} us)", flush=True)
         size *= 4
     if rank == 0 and out_path:

@@ -572,7 +572,8 @@ def allgather_gemm_matches_gathered(rank, world):
         x = torch.randn(M, Kd, device=dev).to(torch.bfloat16)
         bias = torch.randn(N, device=dev).to(torch.bfloat16)
         segs = [(shard_buf.ptrs[r], per * 2) for r in range(world)]
-        spec = K.GatherSpec(segs, N * Kd * 2, dev, chunk_rows=32, row_bytes=Kd * 2)
+        # local-first order: tiles / k-blocks / chunks start at this rank's own shard
+        spec = K.GatherSpec(segs, N * Kd * 2, dev, chunk_rows=32, row_bytes=Kd * 2, local_begin=rank * per * 2)
         w_local = torch.zeros(N, Kd, dtype=torch.bfloat16, device=dev)
         for rep in range(2):   # second call reuses flags with a higher epoch
             w_local.zero_()

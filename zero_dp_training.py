@@ -53,7 +53,18 @@ def train(model_name, batch_size, training_steps, stage, *args, bf16=None, seq_l
 
     cfg = resolve_config(model_name)
     torch.manual_seed(0)
-    model = build_model(cfg)
+    if model_name.startswith("scale:") and on_gpu and bf16 is not False:
+        # multi-billion-parameter shapes are created on the GPU in bf16 directly: an fp32 host copy
+        # per rank (the reference's from_pretrained on the CPU) would be tens of GB times the ranks
+        old = torch.get_default_dtype()
+        torch.set_default_dtype(torch.bfloat16)
+        try:
+            with torch.device(device):
+                model = build_model(cfg)
+        finally:
+            torch.set_default_dtype(old)
+    else:
+        model = build_model(cfg)
     if pretrained:   # local HF checkpoint of the same architecture (the reference downloads it)
         from dtds_b200.models import load_pretrained
         load_pretrained(model, pretrained)
