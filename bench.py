@@ -44,8 +44,6 @@ def parse_args():
     ap.add_argument("--no-overlap-optimizer", action="store_true",
                     help="one Adam launch after backward instead of per-bucket updates under backward")
     ap.add_argument("--adam-bucket-mb", type=float, default=32.0)
-    ap.add_argument("--sparse-embedding-grads", action="store_true",
-                    help="DDP: reduce the tied embedding table early and exchange the lookup rows as (ids, rows)")
     ap.add_argument("--comm", default=None, choices=[None, "custom", "nccl"])
     return ap.parse_args()
 
@@ -257,8 +255,7 @@ def build_ours(args, cfg, dev, world, ids_h, labels_h):
 
     model = build_model(cfg).to(device=dev, dtype=torch.bfloat16)
     model.train()
-    net = DistributedDataParallel(model, device_ids=[dev.index], bucket_cap_mb=args.bucket_size,
-                                  sparse_embedding_grads=args.sparse_embedding_grads or None) if world > 1 else model
+    net = DistributedDataParallel(model, device_ids=[dev.index], bucket_cap_mb=args.bucket_size) if world > 1 else model
     # Adam runs per bucket under backward (after the bucket's all-reduce when world > 1)
     overlap = not args.no_overlap_optimizer
     opt = HFAdamW(model.parameters(), lr=5e-5, overlap_with_backward=overlap and world == 1,

@@ -24,11 +24,10 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--no-graph", action="store_true")
-    ap.add_argument("--sparse-embedding-grads", action="store_true")
     a = ap.parse_args()
     args = argparse.Namespace(gpus=a.gpus, steps=8, warmup=3, impl="ours", model="base", batch_size=4, seq_len=512,
                               bucket_size=25, no_graph=a.no_graph, no_overlap_optimizer=False, adam_bucket_mb=32.0,
-                              sparse_embedding_grads=a.sparse_embedding_grads, comm=None)
+                              comm=None)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)

@@ -75,56 +75,6 @@ embedding_bwd_word_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* 
     }
   }
 }
-// Deterministic variant for rows that every rank must reduce to the same bits (DDP sparse-row
-// exchange): ids arrive sorted ascending together with the permutation that sorted them.  The
-// warp standing on the first position of a run of equal ids sums the run's rows in sorted order in
-// fp32 and is the only writer of that table row: no atomics, one rounding, identical on all ranks.
-__global__ void __launch_bounds__(256)
-embedding_bwd_sorted_kernel(const int64_t* __restrict__ sorted_ids, const int64_t* __restrict__ perm,
-                            const __nv_bfloat16* __restrict__ rows, void* __restrict__ dword, int n,
-                            int hidden, int vocab, int grads_fp32) {
-  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (i >= n) return;
-  const int64_t id = sorted_ids[i];
-  if (id < 0 || id >= vocab) return;
-  if (i > 0 && sorted_ids[i - 1] == id) return;   // not the head of its run
-  const int lane = threadIdx.x & 31;
-  for (int c = lane * 2; c < hidden; c += 64) {
-    float a0 = 0.f, a1 = 0.f;
-    for (int j = i; j < n && sorted_ids[j] == id; ++j) {
-      const uint32_t u = *reinterpret_cast<const uint32_t*>(rows + static_cast<size_t>(perm[j]) * hidden + c);
-      a0 += bf16_lo(u);
-      a1 += bf16_hi(u);
-    }
-    if (grads_fp32) {
-      float* d = static_cast<float*>(dword) + static_cast<size_t>(id) * hidden + c;
-      d[0] += a0;
-      d[1] += a1;
-    } else {
-      __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dword) + static_cast<size_t>(id) * hidden + c;
-      const uint32_t old = *reinterpret_cast<const uint32_t*>(d);
-      *reinterpret_cast<uint32_t*>(d) = pack_bf16x2(bf16_lo(old) + a0, bf16_hi(old) + a1);
-    }
-  }
-}
-// Position-embedding gradient: positions are t % seq, so dpos[s] = sum_b dout[b*seq + s].
-__global__ void embedding_bwd_pos_kernel(const __nv_bfloat16* __restrict__ dout,
-                                         void* __restrict__ dpos, int batch, int seq, int hidden,
-                                         int pos_offset, int grads_fp32, int accumulate) {
-  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (i >= static_cast<size_t>(seq) * hidden) return;
-  float s = 0.f;
-  for (int b = 0; b < batch; ++b) s += __bfloat162float(dout[static_cast<size_t>(b) * seq * hidden + i]);
-  const size_t o = i + static_cast<size_t>(pos_offset) * hidden;
-  if (grads_fp32) {
-    float* d = static_cast<float*>(dpos);
-    d[o] = accumulate ? d[o] + s : s;
-  } else {
-    __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dpos);
-    d[o] = __float2bfloat16(accumulate ? __bfloat162float(d[o]) + s : s);
-  }
-}
-
 // ------------------------------------------------------------------------------------------
 // Cross-entropy over [rows, vocab] bf16 logits with ignore_index, mean reduction.
 //   pass A (ce_count_kernel): n_valid = #(label != ignore).
@@ -395,18 +345,6 @@ extern "C" int dtds_embedding_bwd(const long long* ids, const void* dout, void* 
         accumulate_pos);
     DTDS_HOST_CHECK(cudaGetLastError());
   }
-  return 0;
-}
-
-extern "C" int dtds_embedding_bwd_sorted(const long long* sorted_ids, const long long* perm,
-                                         const void* rows, void* dword, int n, int hidden, int vocab,
-                                         int grads_fp32, cudaStream_t stream) {
-  if (n <= 0) return 0;
-  if (hidden % 2 != 0) return -1;
-  embedding_bwd_sorted_kernel<<<(n + 7) / 8, 256, 0, stream>>>(
-      reinterpret_cast<const int64_t*>(sorted_ids), reinterpret_cast<const int64_t*>(perm),
-      static_cast<const __nv_bfloat16*>(rows), dword, n, hidden, vocab, grads_fp32);
-  DTDS_HOST_CHECK(cudaGetLastError());
   return 0;
 }
 

@@ -164,11 +164,11 @@ class BertForMaskedLM(nn.Module):
         tied = self.embeddings.word_embeddings if cfg.tie_word_embeddings else None
         self.head = BertOnlyMLMHead(cfg, tied_weight=tied)
         if tied is not None:
-            Fn.mark_shared_grad(tied, 2, sparse_rows=True)  # embedding scatter-add + decoder wgrad
+            Fn.mark_shared_grad(tied, 2)  # embedding scatter-add + decoder wgrad
 
     def forward(self, input_ids, labels=None, attention_mask=None, return_logits=False):
         if self.cfg.tie_word_embeddings:
-            Fn.mark_shared_grad(self.embeddings.word_embeddings, 2, sparse_rows=True)   # survives deepcopy
+            Fn.mark_shared_grad(self.embeddings.word_embeddings, 2)   # survives deepcopy
         kb = key_padding_bias(attention_mask)
         h = self.embeddings(input_ids)
         for layer in self.encoders:

@@ -66,7 +66,7 @@ class CausalLM(nn.Module):
         self.final_ln = LayerNorm(H, cfg.layer_norm_eps)
         if cfg.tie_word_embeddings:
             self.lm_head_weight = None
-            Fn.mark_shared_grad(self.word_embeddings, 2, sparse_rows=True)
+            Fn.mark_shared_grad(self.word_embeddings, 2)
         else:
             self.lm_head_weight = nn.Parameter(_init_normal_(torch.empty(cfg.vocab_size, H)))
 
@@ -83,7 +83,7 @@ class CausalLM(nn.Module):
 
     def forward(self, input_ids, labels=None, attention_mask=None, return_logits=False):
         if self.lm_head_weight is None:
-            Fn.mark_shared_grad(self.word_embeddings, 2, sparse_rows=True)   # survives deepcopy
+            Fn.mark_shared_grad(self.word_embeddings, 2)   # survives deepcopy
         kb = key_padding_bias(attention_mask)
         h = self.embed(input_ids)
         for layer in self.layers:

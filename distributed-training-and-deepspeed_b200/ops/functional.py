@@ -86,15 +86,11 @@ def grad_target(param):
     return mg, bool(getattr(param, "_grad_written", False))
 
 
-def mark_shared_grad(param, uses: int, sparse_rows: bool = False) -> None:
+def mark_shared_grad(param, uses: int) -> None:
     """Declares that `uses` backward producers write this parameter's gradient (tied embeddings).
     Models call it at the top of forward, not only in __init__: ``copy.deepcopy`` of a Parameter
     drops Python attributes, and a lost mark would fire the gradient-ready callback (bucket
-    all-reduce / Adam) after the first producer.  ``sparse_rows``: one of the producers is the
-    embedding lookup (EmbeddingFn), whose gradient is a set of rows an engine may exchange as
-    (ids, rows) instead of waiting for it before reducing the dense table."""
-    if sparse_rows:
-        param._sparse_rows_producer = True
+    all-reduce / Adam) after the first producer."""
     if getattr(param, "_grad_uses", 1) != uses:
         from ..parallel.flat import grad_uses
         param._grad_uses = uses
@@ -502,12 +498,7 @@ class EmbeddingFn(torch.autograd.Function):
             K.colsum(dout.view(B * S, H), out=tgt[0], accumulate=True)
             return tgt
 
-        sink = getattr(word, "_sparse_sink", None)
-        if sink is not None and word.requires_grad:
-            sink(word, ids, dout)   # the engine exchanges (ids, rows) and scatter-adds them itself
-            dword = None
-        else:
-            dword = _emit(word, word_compute)
+        dword = _emit(word, word_compute)
         dpos = _emit(pos, pos_compute) if pos is not None else None
         dtyp = _emit(typ, type_compute) if typ is not None else None
         return None, dword, dpos, dtyp, None

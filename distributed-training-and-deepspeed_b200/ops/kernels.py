@@ -370,29 +370,6 @@ def embedding_bwd(ids, dout, dword, dpos=None, pos_offset=0, accumulate_pos=Fals
     _lib.check(rc, "dtds_embedding_bwd")
 
 
-def embedding_bwd_deterministic(ids, rows, dword):
-    """dword[ids[i]] += rows[i] with one writer per table row and run sums in sorted order: the
-    result depends only on the inputs, not on scheduling (replicas that apply it to identical
-    gathered rows stay bit-identical).  ids [n] int64, rows [n, H]."""
-    ids = ids.reshape(-1)
-    H = rows.shape[-1]
-    rows = rows.reshape(-1, H)
-    sorted_ids, perm = torch.sort(ids, stable=True)
-    if not _lib.use_native(rows):
-        head = torch.ones_like(sorted_ids, dtype=torch.bool)
-        head[1:] = sorted_ids[1:] != sorted_ids[:-1]
-        seg = torch.cumsum(head.to(torch.int64), 0) - 1
-        sums = torch.zeros(int(seg[-1]) + 1, H, dtype=torch.float32).index_add_(0, seg, rows[perm].float())
-        uniq = sorted_ids[head]
-        dword[uniq] = (dword[uniq].float() + sums).to(dword.dtype)
-        return
-    rows = _c(rows)
-    rc = _lib.lib().dtds_embedding_bwd_sorted(
-        sorted_ids.data_ptr(), perm.data_ptr(), rows.data_ptr(), dword.data_ptr(), ids.numel(), H,
-        dword.shape[0], int(dword.dtype == torch.float32), _lib.stream_ptr())
-    _lib.check(rc, "dtds_embedding_bwd_sorted")
-
-
 def cross_entropy(logits, labels, *, vocab=None, ignore_index=-100, shift=False, seq=None,
                   want_grad=True, inplace_grad=True, gscale=1.0, n_valid=None):
     """Mean CE over non-ignored rows of logits [R, ld] (first `vocab` columns are real).

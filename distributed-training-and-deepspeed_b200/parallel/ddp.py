@@ -32,14 +32,11 @@ from .flat import FlatBuffers, grad_uses
 
 
 class _Bucket:
-    __slots__ = ("index", "lo", "hi", "params", "pending", "launched", "sparse", "sparse_pending",
-                 "deferred_step")
+    __slots__ = ("index", "lo", "hi", "params", "pending", "launched")
 
     def __init__(self, index):
         self.index, self.lo, self.hi = index, None, None
         self.params, self.pending, self.launched = [], 0, False
-        # sparse: the bucket holds one tied embedding table whose lookup rows arrive separately
-        self.sparse, self.sparse_pending, self.deferred_step = False, False, None
 
 
 def assign_buckets(params, offsets, bucket_cap_mb: float, elem_size: int, first_bucket_mb: float = 1.0,
@@ -75,8 +72,7 @@ def assign_buckets(params, offsets, bucket_cap_mb: float, elem_size: int, first_
 class DistributedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, device_ids=None, bucket_cap_mb: float = 25,
                  process_group=None, grad_dtype: torch.dtype | None = None,
-                 broadcast_parameters: bool = True, comm_blocks: int = 0,
-                 sparse_embedding_grads: bool | None = None):
+                 broadcast_parameters: bool = True, comm_blocks: int = 0):
         super().__init__()
         self.module = module
         self.group = process_group
@@ -102,27 +98,12 @@ class DistributedDataParallel(nn.Module):
         esz = self.flat.grad_flat.element_size()
         self.buckets: list[_Bucket] = []
         self._bucket_of = {}
-        # Tied embedding tables (marked by the models) get their gradient from a dense producer
-        # early in backward and from the embedding lookup at its very end.  In sparse mode the
-        # table's bucket is reduced after the dense producer and the lookup rows are exchanged as
-        # (ids, rows) when they arrive, instead of a table-sized all-reduce that nothing can hide.
-        if sparse_embedding_grads is None:
-            sparse_embedding_grads = os.environ.get("DTDS_SPARSE_EMB_GRAD", "0") not in ("0", "")
-        self.sparse_embedding_grads = bool(sparse_embedding_grads) and self.world > 1
-        solo = set()
-        if self.sparse_embedding_grads:
-            solo = {i for i, p in enumerate(self.flat.params)
-                    if getattr(p, "_sparse_rows_producer", False) and getattr(p, "_grad_uses", 1) > 1}
-        self._sparse_stage = None
         for bi, (idxs, lo, hi) in enumerate(assign_buckets(self.flat.params, self.flat.offsets,
-                                                          bucket_cap_mb, esz, solo=solo)):
+                                                          bucket_cap_mb, esz)):
             b = _Bucket(bi)
             # 16-byte aligned byte range (parameter starts are 64-element aligned)
             b.lo, b.hi = lo, (hi + 63) // 64 * 64
             b.params = [self.flat.params[i] for i in idxs]
-            b.sparse = bool(solo) and idxs[0] in solo
-            b.sparse_pending = False
-            b.deferred_step = None
             self.buckets.append(b)
             for p in b.params:
                 self._bucket_of[id(p)] = b
@@ -140,8 +121,6 @@ class DistributedDataParallel(nn.Module):
         for i, p in enumerate(self.flat.params):
             p._on_grad_ready = self._param_ready
             p.register_post_accumulate_grad_hook(self._autograd_grad_hook)
-            if i in solo:
-                p._sparse_sink = self._sparse_rows
         self._reset_iteration()
 
     # ------------------------------------------------------------------------------ setup
@@ -166,8 +145,6 @@ class DistributedDataParallel(nn.Module):
         for b in self.buckets:
             b.pending = len(b.params)
             b.launched = False
-            b.sparse_pending = b.sparse
-            b.deferred_step = None
         self._events.clear()
         self._callback_queued = False
 
@@ -206,71 +183,7 @@ class DistributedDataParallel(nn.Module):
     def _step_bucket(self, b, stream):
         if self.optimizer is None or self._accumulating:
             return
-        if b.sparse_pending:   # the lookup rows of this table have not been folded in yet
-            b.deferred_step = (stream,)
-            return
         self.optimizer.step_range(self.flat, b.lo, min(b.hi, self.flat.total), stream=stream)
-
-    # ------------------------------------------------------------------ sparse embedding rows
-    def _sparse_rows(self, p, ids, dout):
-        """Called by EmbeddingFn.backward instead of its local scatter-add (sparse mode).  The
-        dense part of the table's gradient (decoder wgrad) has already been all-reduced; here every
-        rank contributes its (ids, rows / world), all ranks gather them and add all of them to the
-        reduced table: 2·T·H bytes per rank on the wire instead of a second look at V·H."""
-        from ..ops import kernels as K
-        b = self._bucket_of[id(p)]
-        T, H = ids.numel(), dout.shape[-1]
-        ids1 = ids.reshape(1, T)
-        rows = dout.reshape(1, T, H)
-        if not self._require_sync or not b.launched or not b.sparse_pending:
-            # accumulation pass, or the dense producer never ran: plain local scatter-add; a later
-            # (or the straggler) all-reduce of the whole bucket covers these rows
-            if not p._grad_written:
-                p.main_grad.zero_()
-                p._grad_written = True
-            K.embedding_bwd(ids1, rows, p.main_grad, None)
-            b.sparse_pending = False
-            return
-        rows = (rows * (1.0 / self.world)).to(dout.dtype)
-        if self._custom:
-            cur = torch.cuda.current_stream(self.device)
-            ready = torch.cuda.Event()
-            ready.record(cur)
-            self._comm_stream.wait_event(ready)
-            ctx = comm.symm_context(self.group)
-            per = (T * H * rows.element_size() + T * 8 + 15) // 16 * 16
-            if self._sparse_stage is None or self._sparse_stage[1] != per:
-                # symmetric staging buffer: allocated on first use (eager warm-up, never in capture)
-                self._sparse_stage = (ctx.new_buffer(per * self.world), per)
-            stage = self._sparse_stage[0]
-            with torch.cuda.stream(self._comm_stream):
-                rows.record_stream(self._comm_stream)
-                packed = torch.empty(per, dtype=torch.uint8, device=self.device)
-                nb_rows = T * H * rows.element_size()
-                packed[:nb_rows].copy_(rows.reshape(-1).view(torch.uint8))
-                packed[nb_rows:nb_rows + T * 8].copy_(ids1.reshape(-1).contiguous().view(torch.uint8))
-                ctx.all_gather(stage, 0, per, packed)
-                allb = stage.tensor(torch.uint8, per * self.world).view(self.world, per)
-                # same rows, same order, one writer per table row on every rank: replicas stay
-                # bit-identical (local atomics would round in a rank-dependent order)
-                g_rows = torch.stack([allb[r, :nb_rows].view(rows.dtype).view(T, H) for r in range(self.world)])
-                g_ids = torch.stack([allb[r, nb_rows:nb_rows + T * 8].view(torch.int64) for r in range(self.world)])
-                K.embedding_bwd_deterministic(g_ids, g_rows, p.main_grad)
-                b.sparse_pending = False
-                if b.deferred_step is not None:
-                    self._step_bucket(b, self._comm_stream)
-                e = torch.cuda.Event()
-                e.record(self._comm_stream)
-            self._events.append(e)
-        else:
-            all_rows = torch.empty(self.world, T, H, dtype=rows.dtype, device=rows.device)
-            all_ids = torch.empty(self.world, T, dtype=torch.int64, device=ids.device)
-            comm.all_gather_into_tensor(all_rows, rows.contiguous(), group=self.group)
-            comm.all_gather_into_tensor(all_ids, ids1.contiguous(), group=self.group)
-            K.embedding_bwd_deterministic(all_ids, all_rows, p.main_grad)
-            b.sparse_pending = False
-            if b.deferred_step is not None:
-                self._step_bucket(b, None)
 
     def _launch_bucket(self, b: _Bucket):
         with nvtx_range(f"ddp.bucket{b.index} all_reduce {(b.hi - b.lo) * self.flat.grad_flat.element_size() >> 10} KiB"):
@@ -315,13 +228,10 @@ class DistributedDataParallel(nn.Module):
             comm.comms_logger.record_events("all_reduce", nbytes, self.world, s, e)
             self._events.append(e)
             if self.optimizer is not None and not self._accumulating:
-                if b.sparse_pending:
-                    self._step_bucket(b, self._comm_stream)    # deferred until the lookup rows are in
-                else:
-                    self._opt_stream.wait_event(e)
-                    self._step_bucket(b, self._opt_stream)
-                    self._opt_event = torch.cuda.Event()
-                    self._opt_event.record(self._opt_stream)
+                self._opt_stream.wait_event(e)
+                self._step_bucket(b, self._opt_stream)
+                self._opt_event = torch.cuda.Event()
+                self._opt_event.record(self._opt_stream)
         else:
             view = g[b.lo:b.hi]
             comm.all_reduce(view, group=self.group, backend="nccl", scale=1.0 / self.world)
@@ -348,10 +258,6 @@ class DistributedDataParallel(nn.Module):
                             p.main_grad.zero_()
                             p._grad_written = True
                     self._launch_bucket(b)
-                if b.sparse_pending:   # the lookup never ran (frozen / unused): nothing to fold in
-                    b.sparse_pending = False
-                    if b.deferred_step is not None:
-                        self._step_bucket(b, b.deferred_step[0])
             if self._custom and self._events:
                 cur = torch.cuda.current_stream(self.device)
                 cur.wait_event(self._events[-1])

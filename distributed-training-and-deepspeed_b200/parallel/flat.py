@@ -25,13 +25,8 @@ def unique_params(params) -> list:
 
 
 def grad_uses(p) -> int:
-    """How many backward producers must report before `p`'s gradient-ready callback fires.  A
-    producer whose rows are handed to an engine sink (EmbeddingFn with `_sparse_sink`) does not
-    count: the engine folds those rows in itself."""
-    n = getattr(p, "_grad_uses", 1)
-    if getattr(p, "_sparse_sink", None) is not None:
-        n -= 1
-    return max(n, 1)
+    """How many backward producers must report before `p`'s gradient-ready callback fires."""
+    return max(getattr(p, "_grad_uses", 1), 1)
 
 
 class FlatBuffers:

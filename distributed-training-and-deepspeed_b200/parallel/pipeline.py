@@ -227,6 +227,11 @@ class PipelineStage:
         finally:
             K.set_seed_offset_tensor(None)
         torch.cuda.synchronize(dev)
+        seen, g.params = set(), []
+        for p in [p for m in self.modules for p in m.parameters()] + list(self.extra_params):
+            if p.requires_grad and id(p) not in seen:
+                seen.add(id(p))
+                g.params.append(p)
         self._graphs = g
 
     def _replay(self, input_ids, labels):
@@ -267,6 +272,10 @@ class PipelineStage:
                     sends.append(dist.isend(g.gx[k], dst=prev_rank, group=self.group))
             for w in sends:
                 w.wait()
+            # what the backward hooks would have told the optimizer: every gradient has been written
+            # (FusedAdam.step zeroes the gradient of parameters that report no write)
+            for p in g.params:
+                p._grad_written = True
             if self.is_last:
                 return torch.stack([l.detach() for l in g.loss]).sum()
         return None

@@ -106,12 +106,6 @@ int dtds_embedding_fwd(const long long* ids, const long long* type_ids, const vo
 int dtds_embedding_bwd(const long long* ids, const void* dout, void* dword, void* dpos, int batch,
                        int seq, int hidden, int pos_offset, int vocab, int grads_fp32,
                        int accumulate_pos, cudaStream_t stream);
-/* Row scatter-add without atomics: ids sorted ascending with the sorting permutation; one writer
- * per table row, fp32 run sums in sorted order (bit-identical on every rank given identical
- * inputs).  Used by the DDP sparse-row exchange; the reference has no counterpart. */
-int dtds_embedding_bwd_sorted(const long long* sorted_ids, const long long* perm, const void* rows,
-                              void* dword, int n, int hidden, int vocab, int grads_fp32,
-                              cudaStream_t stream);
 int dtds_cross_entropy(const void* logits, const long long* labels, void* dlogits, float* stats,
                        float* row_loss, int rows, int vocab, int ld, int seq, int shift,
                        long long ignore_index, float gscale, cudaStream_t stream);

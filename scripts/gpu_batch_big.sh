@@ -9,7 +9,6 @@ TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr
 TAILN=12 CUTN=200 run sweep_N$N python pytorch_allreduce.py --world-size $N --sweep --out gpurun_out/allreduce_sweep_${N}gpu.json
 TAILN=1 run fused_paths_N$N $TR --master-port 29531 bench/fused_paths.py; cp gpurun_out/fused_paths.json gpurun_out/fused_paths_${N}gpu.json 2>/dev/null
 CUTN=2600 TAILN=1 run bench_N$N $TR --master-port 29533 bench.py --gpus $N --steps 20 --warmup 5
-CUTN=2600 TAILN=1 run bench_sparse_N$N $TR --master-port 29535 bench.py --gpus $N --steps 20 --warmup 5 --sparse-embedding-grads
 TAILN=14 CUTN=160 run timeline_N$N $TR --master-port 29534 bench/step_timeline.py --gpus $N
 for st in 0 2 3; do TAILN=4 run zero${st}_N$N $TR --master-port 2955$st zero_dp_training.py --stage $st --training-steps $((20 * N)) --quiet; grep -E "Steady|resident" gpurun_out/zero${st}_N$N.log | cut -c1-220; done
 TMO=400 TAILN=4 run zero3_big_N$N $TR --master-port 29557 zero_dp_training.py --stage 3 --model-name $BIG --training-steps $((10 * N)) --quiet; grep -E "Steady|resident|parameter count" gpurun_out/zero3_big_N$N.log | cut -c1-240

@@ -5,11 +5,8 @@ run() { name=$1; shift; echo "== $name"; timeout 300 "$@" > gpurun_out/$name.log
 W="python -u scripts/run_worker.py"
 run pipe_graphs_never $W pipeline_graphs_match_eager $N nccl 250 4 never
 run pipe_graphs_except_last $W pipeline_graphs_match_eager $N nccl 250 4 except_last
-run ddp_sparse_grad $W ddp_matches_single_process $N nccl 200 0.05 1
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 CUTN=2600 TAILN=1 run bench_N$N $TR --master-port 29533 bench.py --gpus $N --steps 20 --warmup 5
-CUTN=2600 TAILN=1 run bench_sparse_N$N $TR --master-port 29535 bench.py --gpus $N --steps 20 --warmup 5 --sparse-embedding-grads
-TAILN=14 CUTN=160 run timeline_sparse_N$N $TR --master-port 29536 bench/step_timeline.py --gpus $N --sparse-embedding-grads
 TAILN=9 run pp_graph_base_N$N python model_parallel_training.py --device-count $N --training-steps 30 --pipeline --micro-batch-count 4
 for st in 2 3; do TAILN=1 CUTN=600 run standin_zero${st}_N$N $TR --master-port 2954$st bench/baseline_standins.py zero --stage $st; done
 TAILN=1 CUTN=600 run standin_mp_N$N python bench/baseline_standins.py mp --devices $N

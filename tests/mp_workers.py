@@ -206,19 +206,14 @@ def _tiny_bert(dev, dtype, seed=0, dropout=0.0):
     return cfg, build_model(cfg).to(device=dev, dtype=dtype)
 
 
-def ddp_matches_single_process(rank, world, bucket_mb=0.05, sparse=False):
-    """Averaged DDP gradients == gradients of the same model on the concatenated batch.
-    sparse: the tied embedding table is reduced after its dense producer and the lookup rows are
-    exchanged as (ids, rows) at the end of backward (DistributedDataParallel sparse mode)."""
+def ddp_matches_single_process(rank, world, bucket_mb=0.05):
+    """Averaged DDP gradients == gradients of the same model on the concatenated batch."""
     from dtds_b200.parallel.ddp import DistributedDataParallel
     dev = _dev(rank)
     dtype = torch.bfloat16 if dev.type == "cuda" else torch.float32
     cfg, model = _tiny_bert(dev, dtype, seed=rank)  # different init per rank: ctor must broadcast
-    ddp = DistributedDataParallel(model, bucket_cap_mb=bucket_mb, sparse_embedding_grads=sparse)
+    ddp = DistributedDataParallel(model, bucket_cap_mb=bucket_mb)
     assert len(ddp.buckets) > 2
-    if sparse:
-        sb = [b for b in ddp.buckets if b.sparse]
-        assert len(sb) == 1 and len(sb[0].params) == 1 and sb[0].params[0] is model.embeddings.word_embeddings
     _, ref_model = _tiny_bert(dev, dtype, seed=0)
     for a, b in zip(model.parameters(), ref_model.parameters()):
         assert torch.equal(a.detach().cpu(), b.detach().cpu()), "constructor did not broadcast rank 0"
@@ -301,7 +296,7 @@ def optimizer_built_before_ddp_wrap(rank, world):
         assert torch.equal(gathered[r].cpu(), a), f"replica {r} diverged from replica {rank}"
 
 
-def ddp_training_loop(rank, world, use_graph=False, fuse_opt=False, sparse=False):
+def ddp_training_loop(rank, world, use_graph=False, fuse_opt=False):
     """A few optimizer steps under DDP; all ranks must hold identical parameters afterwards.
     fuse_opt: Adam runs per bucket on the communication stream right behind the bucket's
     all-reduce (DistributedDataParallel.fuse_optimizer) and must give the same training curve."""
@@ -312,10 +307,10 @@ def ddp_training_loop(rank, world, use_graph=False, fuse_opt=False, sparse=False
     g = torch.Generator().manual_seed(50 + rank)
     ids, labels = None, None
 
-    def run(fused, graph, dropout, sparse_rows=False):
+    def run(fused, graph, dropout):
         nonlocal ids, labels
         cfg, model = _tiny_bert(dev, dtype, seed=0, dropout=dropout)
-        ddp = DistributedDataParallel(model, bucket_cap_mb=0.1, sparse_embedding_grads=sparse_rows)
+        ddp = DistributedDataParallel(model, bucket_cap_mb=0.1)
         opt = FusedAdam(model.parameters(), lr=1e-3)
         if fused:
             ddp.fuse_optimizer(opt)
@@ -348,8 +343,8 @@ def ddp_training_loop(rank, world, use_graph=False, fuse_opt=False, sparse=False
         return
     # no dropout: the two runs see the same masks anyway, but keep the comparison free of RNG state
     l_plain, w_plain = run(False, False, 0.0)
-    l_fused, w_fused = run(True, use_graph, 0.0, sparse)
-    if dev.type == "cpu" and not sparse:   # sparse mode sums the table gradient in another order
+    l_fused, w_fused = run(True, use_graph, 0.0)
+    if dev.type == "cpu":
         assert torch.equal(w_plain, w_fused)
     skip = 2 if use_graph else 0   # graph warm-up consumed two optimizer steps
     for a, b in zip(l_fused, l_plain[skip:]):

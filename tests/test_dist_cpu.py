@@ -13,17 +13,12 @@ def test_ddp_matches_single_process_gloo():
     run_distributed("ddp_matches_single_process", world=2, backend="gloo")
 
 
-def test_ddp_sparse_embedding_rows_gloo():
-    run_distributed("ddp_matches_single_process", world=2, backend="gloo", args=(0.05, True))
-
-
 def test_ddp_training_loop_gloo():
     run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False,))
 
 
-@pytest.mark.parametrize("sparse", [False, True])
-def test_ddp_fused_optimizer_gloo(sparse):
-    run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False, True, sparse))
+def test_ddp_fused_optimizer_gloo():
+    run_distributed("ddp_training_loop", world=2, backend="gloo", args=(False, True))
 
 
 def test_optimizer_built_before_ddp_wrap_gloo():

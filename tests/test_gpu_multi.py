@@ -27,10 +27,6 @@ def test_ddp_matches_single_process():
     run_distributed("ddp_matches_single_process", world=2, backend="nccl")
 
 
-def test_ddp_sparse_embedding_rows():
-    run_distributed("ddp_matches_single_process", world=2, backend="nccl", args=(0.05, True))
-
-
 @pytest.mark.parametrize("use_graph", [False, True])
 def test_ddp_training_loop(use_graph):
     run_distributed("ddp_training_loop", world=2, backend="nccl", args=(use_graph,))
@@ -39,11 +35,6 @@ def test_ddp_training_loop(use_graph):
 @pytest.mark.parametrize("use_graph", [False, True])
 def test_ddp_fused_optimizer(use_graph):
     run_distributed("ddp_training_loop", world=2, backend="nccl", args=(use_graph, True))
-
-
-@pytest.mark.parametrize("use_graph", [False, True])
-def test_ddp_fused_optimizer_sparse_rows(use_graph):
-    run_distributed("ddp_training_loop", world=2, backend="nccl", args=(use_graph, True, True))
 
 
 @pytest.mark.parametrize("arch", ["bloom-tiny", "bert-tiny"])

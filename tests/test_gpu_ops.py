@@ -196,22 +196,3 @@ def test_cast_roundtrip():
     assert torch.equal(back, lp.float())
 
 
-@pytest.mark.parametrize("fp32", [False, True])
-def test_embedding_bwd_deterministic(fp32):
-    """Sorted, atomics-free row scatter-add: matches index_add_ and is bit-reproducible."""
-    torch.manual_seed(0)
-    V, H, n = 1000, 768, 4096
-    ids = torch.randint(0, V, (n,), device="cuda")
-    ids[:500] = 7                                   # a long run of one id
-    rows = (torch.randn(n, H, device="cuda") * 0.1).to(torch.bfloat16)
-    base = torch.randn(V, H, device="cuda").to(torch.float32 if fp32 else torch.bfloat16)
-    want = base.float().index_add_(0, ids, rows.float())
-    outs = []
-    for _ in range(2):
-        d = base.clone()
-        K.embedding_bwd_deterministic(ids, rows, d)
-        outs.append(d)
-    assert torch.equal(outs[0], outs[1])
-    tol = 1e-4 if fp32 else 2 ** -7
-    err = (outs[0].float() - want).abs().max().item() / (want.abs().max().item() + 1e-6)
-    assert err < tol, err
