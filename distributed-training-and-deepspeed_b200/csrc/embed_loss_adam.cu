@@ -75,6 +75,24 @@ embedding_bwd_word_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* 
     }
   }
 }
+// Position-embedding gradient: positions are t % seq, so dpos[s] = sum_b dout[b*seq + s].
+__global__ void embedding_bwd_pos_kernel(const __nv_bfloat16* __restrict__ dout,
+                                         void* __restrict__ dpos, int batch, int seq, int hidden,
+                                         int pos_offset, int grads_fp32, int accumulate) {
+  const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<size_t>(seq) * hidden) return;
+  float s = 0.f;
+  for (int b = 0; b < batch; ++b) s += __bfloat162float(dout[static_cast<size_t>(b) * seq * hidden + i]);
+  const size_t o = i + static_cast<size_t>(pos_offset) * hidden;
+  if (grads_fp32) {
+    float* d = static_cast<float*>(dpos);
+    d[o] = accumulate ? d[o] + s : s;
+  } else {
+    __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dpos);
+    d[o] = __float2bfloat16(accumulate ? __bfloat162float(d[o]) + s : s);
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // Cross-entropy over [rows, vocab] bf16 logits with ignore_index, mean reduction.
 //   pass A (ce_count_kernel): n_valid = #(label != ignore).
