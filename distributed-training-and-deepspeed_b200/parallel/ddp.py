@@ -209,29 +209,42 @@ class DistributedDataParallel(nn.Module):
             # oriented launch (one block per SM, two vectors in flight per thread).  Earlier buckets
             # use the 64-register variant on 32 SMs' worth of blocks next to the resident GEMM CTAs.
             tail = b.index >= len(self.buckets) - 3
-            with torch.cuda.stream(self._comm_stream):
-                s = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
-                e = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
-                s.record()
-                if self._nvls and nbytes >= (256 << 10) and g.dtype in (torch.bfloat16, torch.float32):
-                    # in-switch reduction: multimem.ld_reduce + multimem.st (csrc/comm_p2p.cu)
-                    from ..comm.symm import all_reduce_nvls
-                    all_reduce_nvls(ctx, self.flat.grad_buf, b.lo * esz, nbytes, g.dtype,
-                                    scale=1.0 / self.world, blocks=self.comm_blocks or (96 if tail else 32))
-                elif tail and not self.comm_blocks:
-                    ctx.all_reduce(self.flat.grad_buf, b.lo * esz, nbytes, g.dtype, scale=1.0 / self.world,
-                                   algo=2, blocks=128)
-                else:
-                    ctx.all_reduce(self.flat.grad_buf, b.lo * esz, nbytes, g.dtype, scale=1.0 / self.world,
-                                   algo=3, blocks=self.comm_blocks)
-                e.record()
-            comm.comms_logger.record_events("all_reduce", nbytes, self.world, s, e)
-            self._events.append(e)
-            if self.optimizer is not None and not self._accumulating:
-                self._opt_stream.wait_event(e)
-                self._step_bucket(b, self._opt_stream)
-                self._opt_event = torch.cuda.Event()
-                self._opt_event.record(self._opt_stream)
+            fused_opt = self.optimizer is not None and not self._accumulating
+            # A large tail bucket (the embedding table: nothing left to overlap it with) is reduced in
+            # pieces so that the Adam update of piece i (HBM-bound, optimizer stream) runs under the
+            # all-reduce of piece i+1 (NVLink-bound, communication stream).
+            lo_hi = [(b.lo, b.hi)]
+            if tail and fused_opt and nbytes >= (16 << 20):
+                k = min(4, nbytes // (8 << 20))
+                step = ((b.hi - b.lo) // k + 64 * self.world - 1) // (64 * self.world) * (64 * self.world)
+                lo_hi = [(lo, min(lo + step, b.hi)) for lo in range(b.lo, b.hi, step)]
+            for lo, hi in lo_hi:
+                nb = (hi - lo) * esz
+                with torch.cuda.stream(self._comm_stream):
+                    s = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
+                    e = torch.cuda.Event(enable_timing=comm.comms_logger.enabled)
+                    s.record()
+                    if self._nvls and nb >= (256 << 10) and g.dtype in (torch.bfloat16, torch.float32):
+                        # in-switch reduction: multimem.ld_reduce + multimem.st (csrc/comm_p2p.cu)
+                        from ..comm.symm import all_reduce_nvls
+                        all_reduce_nvls(ctx, self.flat.grad_buf, lo * esz, nb, g.dtype,
+                                        scale=1.0 / self.world, blocks=self.comm_blocks or (96 if tail else 32))
+                    elif tail and not self.comm_blocks:
+                        # wide, bandwidth-oriented launch: one block per SM, two vectors in flight per thread
+                        ctx.all_reduce(self.flat.grad_buf, lo * esz, nb, g.dtype, scale=1.0 / self.world,
+                                       algo=2, blocks=128)
+                    else:
+                        # 64-register variant on 32 SMs' worth of blocks next to the resident GEMM CTAs
+                        ctx.all_reduce(self.flat.grad_buf, lo * esz, nb, g.dtype, scale=1.0 / self.world,
+                                       algo=3, blocks=self.comm_blocks)
+                    e.record()
+                comm.comms_logger.record_events("all_reduce", nb, self.world, s, e)
+                self._events.append(e)
+                if fused_opt:
+                    self._opt_stream.wait_event(e)
+                    self.optimizer.step_range(self.flat, lo, min(hi, self.flat.total), stream=self._opt_stream)
+                    self._opt_event = torch.cuda.Event()
+                    self._opt_event.record(self._opt_stream)
         else:
             view = g[b.lo:b.hi]
             comm.all_reduce(view, group=self.group, backend="nccl", scale=1.0 / self.world)

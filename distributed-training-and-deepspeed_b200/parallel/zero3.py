@@ -116,26 +116,44 @@ class Zero3ParamManager:
         """Stage 3 shards the gradients too (DeepSpeed stage 3, zero_dp_training.py:41 `--stage 3`):
         a bucket's gradients are dead once its reduce-scatter + Adam kernel has run, which happens
         right behind the backward of the block that produced them.  So instead of a model-sized
-        buffer the gradients live in an arena of `grad_ring_buckets` bucket-sized slots that the
-        buckets take turns using in backward order, plus fixed space for the buckets of parameters
-        that collect gradients over the whole backward (tied embeddings).  A slot is refilled only
-        after the previous user's kernel has completed (event wait in the block's pre-backward hook)."""
+        buffer the gradients live in an arena of `grad_ring_blocks` slots, each large enough for the
+        buckets of one block, that the blocks take turns using in backward order, plus fixed space
+        for the buckets of parameters that collect gradients over the whole backward (tied
+        embeddings, root-level parameters).  A bucket belongs to the block whose backward writes
+        into it first; before that block's backward starts, the stream waits for the kernels of the
+        buckets that used its slot `grad_ring_blocks` blocks earlier (events of the same step)."""
         e, f = self.e, self.flat
         zcfg = e.config.get("zero_optimization", {}) or {}
-        depth = max(2, int(zcfg.get("grad_ring_buckets", 4)))
-        pinned_ids = {id(p) for p in self.pinned.params}
-        ring = [b for b in e.buckets if not any(id(p) in pinned_ids for p in b.params)]
-        fixed = [b for b in e.buckets if any(id(p) in pinned_ids for p in b.params)]
-        slot = max((b.hi - b.lo for b in ring), default=0)
-        slots = min(depth, len(ring))
+        depth = max(2, int(zcfg.get("grad_ring_blocks", 3)))
+        block_of = {}
+        for bi, blk in enumerate(self.blocks):
+            for p in blk.params:
+                block_of[id(p)] = bi
+        fixed, groups = [], {}
+        for b in e.buckets:   # b.params[0] is the bucket's last parameter = its first in backward
+            owners = [block_of.get(id(p)) for p in b.params]
+            if any(o is None for o in owners):
+                fixed.append(b)
+            else:
+                groups.setdefault(max(owners), []).append(b)   # latest block in forward order runs first
+        order = sorted(groups, reverse=True)                   # blocks in backward order
+        slot = max((sum(b.hi - b.lo for b in groups[k]) for k in order), default=0)
+        slots = min(depth, len(order))
         off = 0
         for b in fixed:
             b.goff, b.prev_user = off, None
             off += b.hi - b.lo
         base = off
-        for i, b in enumerate(ring):   # e.buckets is in backward order (last parameters first)
-            b.goff = base + (i % slots) * slot
-            b.prev_user = ring[i - slots] if i >= slots else None
+        self._slot_waits = {}   # block index -> buckets whose kernels must have finished before its backward
+        for n, k in enumerate(order):
+            o = base + (n % slots) * slot
+            for b in groups[k]:
+                b.goff = o
+                o += b.hi - b.lo
+            prev = groups[order[n - slots]] if n >= slots else []
+            for b in groups[k]:
+                b.prev_user = prev[0] if prev else None
+            self._slot_waits[k] = list(prev)
         total = base + slots * slot
         esz = torch.empty((), dtype=f.grad_dtype).element_size()
         if self.custom and f.grad_dtype == torch.bfloat16:
@@ -156,17 +174,17 @@ class Zero3ParamManager:
     def gradient_bytes(self) -> int:
         return self.grads.numel() * self.grads.element_size()
 
-    def _wait_slots(self, blk) -> None:
-        """Before a block's backward writes gradients: the ring slots of its buckets must have been
-        drained by their previous users (stream-ordered; the weight-gradient side stream forks from
-        the current stream after this point)."""
+    def _wait_slots(self, blk_index: int) -> None:
+        """Before a block's backward writes gradients: the previous users of its arena slot must have
+        been drained (stream-ordered; the weight-gradient side stream forks from the current stream
+        after this point).  Their kernels were enqueued earlier in this same backward, so under graph
+        capture these are waits on events of the capture itself."""
         if self.dev.type != "cuda":
             return
         cur = torch.cuda.current_stream(self.dev)
-        for b in blk.buckets:
-            prev = b.prev_user
-            if prev is not None and prev.done_event is not None:
-                cur.wait_event(prev.done_event)
+        for b in self._slot_waits.get(blk_index, ()):
+            if b.done_event is not None and b.launched:
+                cur.wait_event(b.done_event)
 
     def shard_view(self, b) -> torch.Tensor:
         return self.shards[b.state_off:b.state_off + b.per]
@@ -304,7 +322,7 @@ class Zero3ParamManager:
 
     def _pre_bwd(self, blk, idx):
         def hook(module, grad_output):
-            self._wait_slots(blk)
+            self._wait_slots(idx)
             self._materialize(blk)
             self._prefetch(idx - 1)
         return hook

@@ -356,8 +356,8 @@ def _ds_config(stage, bf16):
     return {"train_micro_batch_size_per_gpu": 2,
             "optimizer": {"type": "Adam", "params": {"lr": 1e-3}},
             "comms_logger": {"enabled": True, "verbose": False, "prof_all": True, "debug": False},
-            # small buckets and a 2-slot gradient ring: stage 3 reuses every slot several times per step
-            "zero_optimization": {"stage": stage, "reduce_bucket_size": 3e4, "grad_ring_buckets": 2},
+            # small buckets and a 2-block gradient ring: stage 3 reuses every slot several times per step
+            "zero_optimization": {"stage": stage, "reduce_bucket_size": 3e4, "grad_ring_blocks": 2},
             "bf16": {"enabled": bf16}}
 
 
