@@ -210,11 +210,12 @@ class DistributedDataParallel(nn.Module):
             # use the 64-register variant on 32 SMs' worth of blocks next to the resident GEMM CTAs.
             tail = b.index >= len(self.buckets) - 3
             fused_opt = self.optimizer is not None and not self._accumulating
-            # A large tail bucket (the embedding table: nothing left to overlap it with) is reduced in
-            # pieces so that the Adam update of piece i (HBM-bound, optimizer stream) runs under the
-            # all-reduce of piece i+1 (NVLink-bound, communication stream).
+            # Splitting a large tail bucket so that Adam of piece i runs under the all-reduce of piece
+            # i+1 was measured (2 B200s): the wide all-reduce blocks and the Adam blocks do not fit on
+            # an SM together, the pieces serialise and each pays the kernel's latency (5.39 vs 5.26
+            # ms/step).  Kept behind DTDS_DDP_TAIL_CHUNKS for experiments; one piece by default.
             lo_hi = [(b.lo, b.hi)]
-            if tail and fused_opt and nbytes >= (16 << 20):
+            if tail and fused_opt and nbytes >= (16 << 20) and os.environ.get("DTDS_DDP_TAIL_CHUNKS", "0") != "0":
                 k = min(4, nbytes // (8 << 20))
                 step = ((b.hi - b.lo) // k + 64 * self.world - 1) // (64 * self.world) * (64 * self.world)
                 lo_hi = [(lo, min(lo + step, b.hi)) for lo in range(b.lo, b.hi, step)]

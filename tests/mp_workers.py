@@ -583,7 +583,10 @@ def allgather_gemm_matches_gathered(rank, world):
         dx = K.gemm_allgather(dy, w_local, spec, b_mn_major=True)
         torch.cuda.synchronize()
         want = K.gemm(dy, w_full, b_mn_major=True)
-        assert torch.equal(dx, want), ("dgrad", M, N, Kd)
+        # the k-blocks are visited starting at this rank's own shard: same products, another fp32
+        # summation order, so the bf16 results may differ in the last bit
+        err = (dx.float() - want.float()).abs().max().item()
+        assert err <= 2 ** -6 * want.float().abs().max().item(), ("dgrad", M, N, Kd, err)
         dist.barrier()
 
 
