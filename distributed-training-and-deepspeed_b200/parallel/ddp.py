@@ -48,14 +48,24 @@ def assign_buckets(params, offsets, bucket_cap_mb: float, elem_size: int, first_
     first = int(first_bucket_mb * 1024 * 1024) // elem_size
     out, cur, cur_elems = [], [], 0
     limit = min(first, cap) if first > 0 else cap
+    # The parameters assigned last are the ones whose gradients arrive last: their buckets cannot
+    # hide behind any compute.  Once no more than one cap's worth of ordinary parameters is left,
+    # the cap drops to half of that remainder, so only a small bucket sits at the very end.
+    remaining = sum(p.numel() for p in params if p.numel() <= cap)
+    tail_cap = None
     for i in reversed(range(len(params))):
         n = params[i].numel()
         alone = i in solo
-        if cur and (cur_elems + n > limit or alone):
+        if tail_cap is None and remaining <= cap and n <= cap:
+            tail_cap = max(remaining // 2, min(first, cap) if first > 0 else 1)
+        eff = limit if tail_cap is None else min(limit, tail_cap)
+        if cur and (cur_elems + n > eff or alone):
             out.append(cur)
             cur, cur_elems, limit = [], 0, cap
         cur.append(i)
         cur_elems += n
+        if n <= cap:
+            remaining -= n
         if alone:
             out.append(cur)
             cur, cur_elems, limit = [], 0, cap
