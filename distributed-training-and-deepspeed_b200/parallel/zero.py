@@ -278,6 +278,10 @@ class ZeroEngine(nn.Module):
             self._launch_bucket(b, overlap=self.overlap_comm)
 
     def _end_of_backward(self):
+        if self.param3 is not None and any(not b.launched for b in self.buckets):
+            # stage 3: a bucket without gradients gets zeroed below, in an arena slot that later
+            # blocks may have used in the meantime; their kernels must have drained it first
+            self._join_comm()
         for b in self.buckets:
             if not b.launched:
                 for p in b.params:

@@ -127,3 +127,29 @@ def test_attention_padded_to_block_multiple_matches_unpadded(causal):
     (got * g).sum().backward()
     torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(qkv.grad, gw, rtol=1e-4, atol=1e-6)
+
+
+def test_ddp_bucket_assignment_splits_the_tail():
+    """Reverse-order buckets with a MiB cap; the last cap's worth of ordinary parameters is split so
+    that only a small bucket is left at the very end of backward; oversize parameters sit alone."""
+    import torch
+    from dtds_b200.parallel.ddp import assign_buckets
+    sizes = [30_000_000] + [2_000_000] * 40          # an oversize table first, then 40 ordinary weights
+    params = [torch.nn.Parameter(torch.empty(0)) for _ in sizes]
+    for p, n in zip(params, sizes):
+        p.numel = (lambda n=n: n)                    # sizes only: no storage needed
+    offs, o = [], 0
+    for n in sizes:
+        offs.append(o)
+        o += n
+    cap_mb, esz = 25, 2
+    cap = cap_mb * 1024 * 1024 // esz
+    buckets = assign_buckets(params, offs, cap_mb, esz)
+    covered = sorted(i for idxs, _, _ in buckets for i in idxs)
+    assert covered == list(range(len(sizes))), "every parameter in exactly one bucket"
+    assert buckets[-1][0] == [0], "the oversize parameter is the last bucket, alone"
+    dense = [sum(sizes[i] for i in idxs) for idxs, _, _ in buckets[:-1]]
+    assert all(n <= cap for n in dense)
+    assert dense[-1] <= cap // 2 + 2_000_000, f"tail bucket not split: {dense[-3:]}"
+    for idxs, lo, hi in buckets:                     # contiguous ranges in the flat layout
+        assert lo == min(offs[i] for i in idxs) and hi == max(offs[i] + sizes[i] for i in idxs)
