@@ -286,7 +286,12 @@ def optimizer_built_before_ddp_wrap(rank, world):
         return torch.cat([p.detach().float().flatten() for p in model.parameters()]).cpu()
 
     a, b = run(True), run(False)
-    assert torch.equal(a, b), f"optimizer-first differs from wrap-first by {(a - b).abs().max().item()}"
+    # Adam's first steps move every weight by ~lr whatever the gradient's size, so one last-bit
+    # difference in a near-zero gradient (CPU reductions change their split under load) flips a step
+    # of 2*lr; the bug this guards against (masters taken from the rank's own pre-broadcast weights)
+    # changes essentially every element on the non-zero ranks.
+    frac = ((a - b).abs() > 1e-6).float().mean().item()
+    assert frac < 0.01, f"optimizer-first differs from wrap-first in {frac:.1%} of the elements"
     parts = [torch.empty_like(a) for _ in range(world)] if dev.type != "cuda" else None
     import torch.distributed as dist
     mine = a.to(dev) if dev.type == "cuda" else a
