@@ -90,6 +90,9 @@ class DistributedDataParallel(nn.Module):
         self.rank = comm.get_rank(process_group)
         self.bucket_cap_mb = bucket_cap_mb
         self.comm_blocks = comm_blocks
+        # blocks of the all-reduce kernels that run next to backward's GEMMs (default 32: enough
+        # loads in flight for ~100 GB/s per direction while leaving the SMs to the GEMM CTAs)
+        self._overlap_blocks = int(os.environ.get("DTDS_DDP_OVERLAP_BLOCKS", "0") or 0)
         params = [p for p in module.parameters() if p.requires_grad]
         p0 = params[0]
         self.device = p0.device
@@ -239,7 +242,8 @@ class DistributedDataParallel(nn.Module):
                         # in-switch reduction: multimem.ld_reduce + multimem.st (csrc/comm_p2p.cu)
                         from ..comm.symm import all_reduce_nvls
                         all_reduce_nvls(ctx, self.flat.grad_buf, lo * esz, nb, g.dtype,
-                                        scale=1.0 / self.world, blocks=self.comm_blocks or (96 if tail else 32))
+                                        scale=1.0 / self.world,
+                                        blocks=self.comm_blocks or (96 if tail else (self._overlap_blocks or 32)))
                     elif tail and not self.comm_blocks:
                         # wide, bandwidth-oriented launch: one block per SM, two vectors in flight per thread
                         ctx.all_reduce(self.flat.grad_buf, lo * esz, nb, g.dtype, scale=1.0 / self.world,
@@ -247,7 +251,7 @@ class DistributedDataParallel(nn.Module):
                     else:
                         # 64-register variant on 32 SMs' worth of blocks next to the resident GEMM CTAs
                         ctx.all_reduce(self.flat.grad_buf, lo * esz, nb, g.dtype, scale=1.0 / self.world,
-                                       algo=3, blocks=self.comm_blocks)
+                                       algo=3, blocks=self.comm_blocks or self._overlap_blocks)
                     e.record()
                 comm.comms_logger.record_events("all_reduce", nb, self.world, s, e)
                 self._events.append(e)
