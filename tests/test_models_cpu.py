@@ -259,3 +259,38 @@ def test_zero_engine_rejects_ds_config_keys_it_does_not_implement():
     eng, opt, _, _ = zero.initialize(model=m, model_parameters=m.parameters(),
                                      config={**base, "gradient_accumulation_steps": 1, "gradient_clipping": 0.0})
     assert eng.zero_optimization_stage() == 0
+
+
+def test_checkpoint_replays_fused_dropout_seed_stream():
+    """ops.functional.checkpoint: recomputation regenerates the masks of the first forward (the seed
+    stream is replayed) and leaves the stream where other consumers moved it in the meantime."""
+    import torch
+    from dtds_b200.models import get_config
+    from dtds_b200.models.bert import BertLayer
+    from dtds_b200.ops import functional as Fn
+    cfg = get_config("bert-tiny").replace(hidden_dropout_prob=0.3, attention_probs_dropout_prob=0.3)
+    torch.manual_seed(0)
+    layers = torch.nn.ModuleList([BertLayer(cfg) for _ in range(2)]).train()
+    x0 = torch.randn(2, 128, cfg.hidden_size)
+
+    def run(h):
+        for m in layers:
+            h = m(h)
+        return h
+
+    res = {}
+    for mode in ("plain", "checkpoint"):
+        for p in layers.parameters():
+            p.grad = None
+        Fn.manual_seed(5)
+        x = x0.clone().requires_grad_(True)
+        y = run(x) if mode == "plain" else Fn.checkpoint(run, x)
+        mark = Fn.next_seed()                 # another consumer between forward and backward
+        (y ** 2).mean().backward()
+        after = Fn.get_seed_state()
+        res[mode] = (y.detach(), x.grad, [p.grad.clone() for p in layers.parameters()], mark, after)
+    assert res["plain"][3] == res["checkpoint"][3] and res["plain"][4] == res["checkpoint"][4], "seed stream position changed"
+    assert torch.allclose(res["plain"][0], res["checkpoint"][0], atol=1e-6)
+    assert torch.allclose(res["plain"][1], res["checkpoint"][1], atol=1e-5), "input gradient changed under recomputation"
+    for a, b in zip(res["plain"][2], res["checkpoint"][2]):
+        assert torch.allclose(a, b, atol=1e-5), "parameter gradient changed under recomputation"
